@@ -1,0 +1,99 @@
+/*
+ * lora_b200.h -- C ABI of the B200 (sm_100a) fused LoRA-linear library.
+ *
+ * The reference (SalahElshafey/VT-Cluster...) has no native boundary of its
+ * own: its LoRA arithmetic is third-party peft `lora.Linear` running on torch
+ * CPU, reached through
+ *     LoraConfig(...) / get_peft_model(...)
+ *         Cluster/Project 1 - Fine Tuning Distilgpt2/finetune_lora_distilgpt2.py:98-104
+ *         Cluster/Project 2 - Course Project/finetune_lora_opt_pp.py:104-112
+ * Each entry point below names the peft/torch step it replaces.  All pointers
+ * are DEVICE pointers unless stated; every buffer (workspace included) is owned
+ * by the caller; calls are asynchronous on `stream`; nothing is retained after
+ * return.  Functions return 0 on success, non-zero on error with a
+ * thread-local message available from lora_last_error().  There is no CPU
+ * path and no fallback: unsupported input is an error.
+ *
+ * Shapes: X [M,K], Y [M,N], W [N,K] (nn.Linear) or [K,N] (GPT-2 Conv1D,
+ * w_is_KN=1), bias [N] or NULL, A [r,K] fp32, B [N,r] fp32, H [M,r_pad],
+ * keep_mask [M,K/8] bytes (bit e of byte (m,k/8) = element (m, 8*(k/8)+e)
+ * survived dropout).  Activations, W and bias are bf16 (dtype 0) or fp16
+ * (dtype 1); accumulation is fp32.  K and N must be multiples of 8,
+ * 1 <= r <= 64.
+ */
+#ifndef LORA_B200_H_
+#define LORA_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef __CUDA_RUNTIME_API_H__
+typedef struct CUstream_st* cudaStream_t;
+#endif
+
+#define LORA_B200_DTYPE_BF16 0
+#define LORA_B200_DTYPE_FP16 1
+
+/* Message for the last failing call made by this host thread ("" if none). */
+const char* lora_last_error(void);
+
+/* Rank padded to the tensor-core K granule the kernels use: 16, 32 or 64. */
+int32_t lora_linear_rpad(int32_t r);
+
+/* Bytes of caller-owned scratch that lora_linear_fwd / lora_linear_bwd need. */
+size_t lora_linear_workspace_bytes(int64_t M, int64_t K, int64_t N, int32_t r);
+
+/*
+ * Forward of one LoRA-adapted projection; replaces peft lora.Linear.forward
+ * (base_layer(x) + lora_B(lora_A(lora_dropout(x))) * scaling) as invoked for
+ * every module matched by target_modules (finetune_lora_distilgpt2.py:100,
+ * finetune_lora_opt_pp.py:109):
+ *     H = dropout_p(X) A^T          (written to H, 16-bit, saved for backward)
+ *     Y = X W^T + bias + scaling * H B^T
+ * p > 0 draws the dropout mask from Philox4x32-10 keyed by (seed, offset) and
+ * writes the keep-bits to keep_mask (needed by backward); p == 0 ignores
+ * keep_mask (may be NULL).
+ */
+int lora_linear_fwd(const void* X, const void* W, const void* bias, const float* A, const float* B, void* Y, void* H,
+                    uint8_t* keep_mask, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p,
+                    uint64_t seed, uint64_t offset, int32_t dtype, int32_t w_is_KN, void* workspace,
+                    size_t workspace_bytes, cudaStream_t stream);
+
+/*
+ * Backward of the same projection; replaces what torch autograd derives from
+ * peft's forward (no custom backward exists in the reference):
+ *     dH = scaling * dY B                 dX = dY W + keep/(1-p) .* (dH A)
+ *     dB = scaling * dY^T H               dA = dH^T dropout_p(X)
+ * No dW, no dbias (base layer frozen, LoraConfig bias="none").  dX may be NULL
+ * (input needs no gradient).  dA [r,K] and dB [N,r] are fp32 and are
+ * overwritten, or added to when accumulate != 0.
+ */
+int lora_linear_bwd(const void* dY, const void* X, const void* W, const float* A, const float* B, const void* H,
+                    const uint8_t* keep_mask, void* dX, float* dA, float* dB, int64_t M, int64_t K, int64_t N,
+                    int32_t r, float scaling, float p, int32_t dtype, int32_t w_is_KN, int32_t accumulate,
+                    void* workspace, size_t workspace_bytes, cudaStream_t stream);
+
+/*
+ * Frozen projection alone, Y = X W^T + bias: the base_layer call of peft's
+ * forward (torch addmm for Conv1D, F.linear for nn.Linear) and what a merged
+ * or disabled adapter reduces to.  Same kernel with the low-rank K-block off.
+ */
+int lora_linear_base(const void* X, const void* W, const void* bias, void* Y, int64_t M, int64_t K, int64_t N,
+                     int32_t dtype, int32_t w_is_KN, cudaStream_t stream);
+
+/*
+ * Dropout keep-bits alone for an [M,K] input (K % 8 == 0): the mask
+ * lora_linear_fwd would draw for the same (p, seed, offset).  Test hook for
+ * checking the device generator against oracle/philox.py.
+ */
+int lora_dropout_keep_mask(uint8_t* keep_mask, int64_t M, int64_t K, float p, uint64_t seed, uint64_t offset,
+                           cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LORA_B200_H_ */

@@ -1,0 +1,153 @@
+"""ctypes binding of liblora_b200.so (C ABI in include/lora_b200.h).
+
+PyTorch is used for device memory and streams only: every call passes raw
+device pointers and the current CUDA stream.  There is no CPU path -- if the
+shared library is missing or fails to load, importing the product fails loudly.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_uint64, c_void_p
+
+import torch
+
+from ._build import LIB_PATH
+
+DTYPE_BF16 = 0
+DTYPE_FP16 = 1
+
+_lib = None
+
+_SIGNATURES = {
+    "lora_last_error": (c_char_p, []),
+    "lora_linear_rpad": (c_int32, [c_int32]),
+    "lora_linear_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64, c_int32]),
+    "lora_linear_fwd": (
+        c_int,
+        [c_void_p] * 8 + [c_int64, c_int64, c_int64, c_int32, c_float, c_float, c_uint64, c_uint64, c_int32, c_int32,
+                          c_void_p, c_size_t, c_void_p],
+    ),
+    "lora_linear_bwd": (
+        c_int,
+        [c_void_p] * 10 + [c_int64, c_int64, c_int64, c_int32, c_float, c_float, c_int32, c_int32, c_int32, c_void_p,
+                           c_size_t, c_void_p],
+    ),
+    "lora_linear_base": (c_int, [c_void_p] * 4 + [c_int64, c_int64, c_int64, c_int32, c_int32, c_void_p]),
+    "lora_dropout_keep_mask": (c_int, [c_void_p, c_int64, c_int64, c_float, c_uint64, c_uint64, c_void_p]),
+}
+
+
+def exported_symbols():
+    """Names declared in include/lora_b200.h (used by the CPU-side ABI test)."""
+    return sorted(_SIGNATURES)
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'`. "
+                "There is no CPU or PyTorch fallback for the fused LoRA kernels."
+            )
+        handle = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(handle, name)  # AttributeError here = ABI drift, fail loudly
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def _check(rc: int, what: str):
+    if rc != 0:
+        raise RuntimeError(f"{what}: {lib().lora_last_error().decode()}")
+
+
+def dtype_code(dt: torch.dtype) -> int:
+    if dt == torch.bfloat16:
+        return DTYPE_BF16
+    if dt == torch.float16:
+        return DTYPE_FP16
+    raise RuntimeError(f"fused LoRA kernels compute in bf16 or fp16 with fp32 accumulation; got {dt}")
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and (not t.is_cuda or not t.is_contiguous()):
+            raise RuntimeError("fused LoRA kernels need contiguous CUDA tensors (no CPU fallback)")
+
+
+def rpad(r: int) -> int:
+    return int(lib().lora_linear_rpad(int(r)))
+
+
+def workspace_bytes(M: int, K: int, N: int, r: int) -> int:
+    return int(lib().lora_linear_workspace_bytes(M, K, N, r))
+
+
+def linear_fwd(x2d, W, bias, A, B, scaling, p, seed, offset, w_is_KN, workspace, out=None):
+    """Y, H, keep = fused forward.  x2d [M,K] 16-bit, A [r,K] / B [N,r] fp32."""
+    _need_cuda(x2d, W, bias, A, B, workspace)
+    M, K = x2d.shape
+    N = W.shape[1] if w_is_KN else W.shape[0]
+    r = A.shape[0]
+    Y = out if out is not None else torch.empty((M, N), dtype=x2d.dtype, device=x2d.device)
+    H = torch.empty((M, rpad(r)), dtype=x2d.dtype, device=x2d.device)
+    keep = torch.empty((M, K // 8), dtype=torch.uint8, device=x2d.device) if p > 0 else None
+    rc = lib().lora_linear_fwd(
+        _ptr(x2d), _ptr(W), _ptr(bias), _ptr(A), _ptr(B), _ptr(Y), _ptr(H), _ptr(keep), M, K, N, r, float(scaling),
+        float(p), int(seed), int(offset), dtype_code(x2d.dtype), int(bool(w_is_KN)), _ptr(workspace),
+        workspace.numel() * workspace.element_size(), _stream(),
+    )
+    _check(rc, "lora_linear_fwd")
+    return Y, H, keep
+
+
+def linear_bwd(dy2d, x2d, W, A, B, H, keep, scaling, p, w_is_KN, workspace, need_dx=True, dA=None, dB=None,
+               accumulate=False):
+    """dX (or None), dA [r,K] fp32, dB [N,r] fp32."""
+    _need_cuda(dy2d, x2d, W, A, B, H, keep, workspace)
+    M, K = x2d.shape
+    N = dy2d.shape[1]
+    r = A.shape[0]
+    dX = torch.empty_like(x2d) if need_dx else None
+    if dA is None:
+        dA = torch.empty((r, K), dtype=torch.float32, device=x2d.device)
+    if dB is None:
+        dB = torch.empty((N, r), dtype=torch.float32, device=x2d.device)
+    rc = lib().lora_linear_bwd(
+        _ptr(dy2d), _ptr(x2d), _ptr(W), _ptr(A), _ptr(B), _ptr(H), _ptr(keep), _ptr(dX), _ptr(dA), _ptr(dB), M, K, N,
+        r, float(scaling), float(p), dtype_code(x2d.dtype), int(bool(w_is_KN)), int(bool(accumulate)),
+        _ptr(workspace), workspace.numel() * workspace.element_size(), _stream(),
+    )
+    _check(rc, "lora_linear_bwd")
+    return dX, dA, dB
+
+
+def linear_base(x2d, W, bias, w_is_KN):
+    """Y = X W^T + bias through the same tcgen05 kernel (adapter disabled / merged)."""
+    _need_cuda(x2d, W, bias)
+    M, K = x2d.shape
+    N = W.shape[1] if w_is_KN else W.shape[0]
+    Y = torch.empty((M, N), dtype=x2d.dtype, device=x2d.device)
+    rc = lib().lora_linear_base(_ptr(x2d), _ptr(W), _ptr(bias), _ptr(Y), M, K, N, dtype_code(x2d.dtype),
+                                int(bool(w_is_KN)), _stream())
+    _check(rc, "lora_linear_base")
+    return Y
+
+
+def dropout_keep_mask(M, K, p, seed, offset, device="cuda"):
+    keep = torch.empty((M, K // 8), dtype=torch.uint8, device=device)
+    rc = lib().lora_dropout_keep_mask(_ptr(keep), M, K, float(p), int(seed), int(offset), _stream())
+    _check(rc, "lora_dropout_keep_mask")
+    return keep

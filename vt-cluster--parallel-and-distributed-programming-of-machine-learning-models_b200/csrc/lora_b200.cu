@@ -1,0 +1,444 @@
+// C-ABI entry points of liblora_b200.so (declared in include/lora_b200.h) and
+// the host-side launch logic: tensor-map encoding, workspace carving, kernel
+// sequencing.  Replaces the peft lora.Linear forward and its autograd backward
+// that the reference reaches through get_peft_model
+// (finetune_lora_distilgpt2.py:98-104, finetune_lora_opt_pp.py:104-112).
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "gemm_sm100.cuh"
+#include "lora_b200.h"
+#include "skinny.cuh"
+
+namespace {
+
+using namespace lb;
+
+thread_local std::string g_err;
+
+int fail(const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return 1;
+}
+
+#define CUDA_TRY(expr)                                                                      \
+  do {                                                                                      \
+    cudaError_t e__ = (expr);                                                               \
+    if (e__ != cudaSuccess) return fail("%s failed: %s", #expr, cudaGetErrorString(e__));  \
+  } while (0)
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      f = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(f);
+  }();
+  return fn;
+}
+
+// 2-D row-major tensor [outer, inner] of 16-bit elements, row stride in elements.
+int make_tmap(CUtensorMap* tm, const void* ptr, int dtype, uint64_t inner, uint64_t outer, uint64_t row_stride_elems,
+              uint32_t box_inner, uint32_t box_outer, CUtensorMapSwizzle sw, const char* what) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return fail("cuTensorMapEncodeTiled not available from the driver");
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15u) != 0) return fail("%s: pointer not 16-byte aligned", what);
+  if ((row_stride_elems * 2) % 16 != 0) return fail("%s: row stride not a multiple of 16 bytes", what);
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {row_stride_elems * 2};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  const CUtensorMapDataType dt = dtype == kDtypeBf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  CUresult r = fn(tm, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled(%s) failed with CUresult %d", what, (int)r);
+  return 0;
+}
+
+CUtensorMapSwizzle swizzle_for_row_bytes(int bytes) {
+  return bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : (bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+constexpr int kMaxDevices = 64;
+struct DeviceInfo {
+  std::atomic<int> ready{0};
+  int sm_count = 0;
+};
+DeviceInfo g_dev[kMaxDevices];
+
+template <typename K>
+cudaError_t opt_in_smem(K kernel, int bytes) {
+  return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+
+// Per-device one-time set-up (SM count, >48 KiB dynamic smem opt-in).  Safe to race.
+int device_setup(int* sm_count) {
+  int dev = 0;
+  CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail("device ordinal %d out of range", dev);
+  DeviceInfo& d = g_dev[dev];
+  if (!d.ready.load(std::memory_order_acquire)) {
+    int major = 0, sms = 0;
+    CUDA_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    if (major != 10) return fail("this library contains sm_100a code only; device %d is compute capability %d.x", dev, major);
+    CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel, gemm::SMEM_BYTES));
+#define OPT_IN_SKINNY(BF, RP)                                                                     \
+  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP>, skinny::rp_smem_bytes<RP>()));             \
+  CUDA_TRY(opt_in_smem(skinny::colproj_kernel<BF, RP>, skinny::cp_smem_bytes<RP>()));
+    OPT_IN_SKINNY(true, 16) OPT_IN_SKINNY(true, 32) OPT_IN_SKINNY(true, 64)
+    OPT_IN_SKINNY(false, 16) OPT_IN_SKINNY(false, 32) OPT_IN_SKINNY(false, 64)
+#undef OPT_IN_SKINNY
+    d.sm_count = sms;
+    d.ready.store(1, std::memory_order_release);
+  }
+  *sm_count = d.sm_count;
+  return 0;
+}
+
+int rpad_of(int r) { return r <= 16 ? 16 : (r <= 32 ? 32 : 64); }
+size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
+
+struct Split {
+  int splits;
+  int rows_per_split;
+};
+// Row splits of the column projections; sized for 148 SMs on purpose so that
+// the workspace size does not depend on the device queried.
+Split colproj_split(int64_t M, int64_t C) {
+  const int64_t c_tiles = (C + skinny::CP_BC - 1) / skinny::CP_BC;
+  const int64_t m_tiles = (M + skinny::CP_BM - 1) / skinny::CP_BM;
+  int64_t want = (2 * 148 + c_tiles - 1) / c_tiles;
+  if (want < 1) want = 1;
+  if (want > m_tiles) want = m_tiles;
+  const int64_t tiles_per = (m_tiles + want - 1) / want;
+  Split s;
+  s.rows_per_split = static_cast<int>(tiles_per * skinny::CP_BM);
+  s.splits = static_cast<int>((M + s.rows_per_split - 1) / s.rows_per_split);
+  return s;
+}
+
+struct Workspace {
+  size_t a16, a16t, sb16, sb16t, dh, partial, total;
+};
+Workspace carve(int64_t M, int64_t K, int64_t N, int r) {
+  const int rp = rpad_of(r);
+  Workspace w;
+  size_t off = 0;
+  w.a16 = off;   off += align256(static_cast<size_t>(rp) * K * 2);
+  w.a16t = off;  off += align256(static_cast<size_t>(rp) * K * 2);
+  w.sb16 = off;  off += align256(static_cast<size_t>(rp) * N * 2);
+  w.sb16t = off; off += align256(static_cast<size_t>(rp) * N * 2);
+  w.dh = off;    off += align256(static_cast<size_t>(M) * rp * 2);
+  const Split sk = colproj_split(M, K), sn = colproj_split(M, N);
+  const size_t pk = static_cast<size_t>(sk.splits) * K * rp * 4, pn = static_cast<size_t>(sn.splits) * N * rp * 4;
+  w.partial = off; off += align256(pk > pn ? pk : pn);
+  w.total = off;
+  return w;
+}
+
+int check_common(int64_t M, int64_t K, int64_t N, int r, int dtype) {
+  if (M <= 0 || K <= 0 || N <= 0) return fail("M, K, N must be positive (got %lld, %lld, %lld)", (long long)M, (long long)K, (long long)N);
+  if (M > INT32_MAX || K > INT32_MAX || N > INT32_MAX) return fail("dimension exceeds 2^31-1");
+  if (K % 8 != 0 || N % 8 != 0) return fail("K and N must be multiples of 8 (16-byte rows for TMA); got K=%lld N=%lld", (long long)K, (long long)N);
+  if (r < 1 || r > 64) return fail("rank r must be in [1, 64]; got %d", r);
+  if (dtype != kDtypeBf16 && dtype != kDtypeFp16) return fail("dtype must be 0 (bf16) or 1 (fp16); fp32 is not supported");
+  return 0;
+}
+
+int launch_pack(const float* A, const float* B, uint8_t* ws, const Workspace& w, int64_t K, int64_t N, int r, float s,
+                int dtype, cudaStream_t stream) {
+  const int rp = rpad_of(r);
+  const long long total = static_cast<long long>(rp) * (K + N);
+  const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, 2048));
+  if (dtype == kDtypeBf16)
+    skinny::pack_adapters_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(
+        A, B, (__nv_bfloat16*)(ws + w.a16), (__nv_bfloat16*)(ws + w.a16t), (__nv_bfloat16*)(ws + w.sb16),
+        (__nv_bfloat16*)(ws + w.sb16t), (int)K, (int)N, r, rp, s);
+  else
+    skinny::pack_adapters_kernel<__half><<<grid, 256, 0, stream>>>(A, B, (__half*)(ws + w.a16), (__half*)(ws + w.a16t),
+                                                                    (__half*)(ws + w.sb16), (__half*)(ws + w.sb16t),
+                                                                    (int)K, (int)N, r, rp, s);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+template <bool BF, int RP>
+int launch_rowproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmP, const skinny::RowProjParams& p,
+                     cudaStream_t stream) {
+  const int grid = (p.M + skinny::RP_BM - 1) / skinny::RP_BM;
+  skinny::rowproj_kernel<BF, RP><<<grid, skinny::RP_THREADS, skinny::rp_smem_bytes<RP>(), stream>>>(tmAct, tmP, p);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// out[M, rp] = out_scale * (keep .* act)[M, C] * P[rp, C]^T
+int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out, int64_t M, int64_t C, int rp,
+                   int dtype, float out_scale, float p, uint64_t seed, uint64_t offset, cudaStream_t stream) {
+  CUtensorMap tmAct, tmP;
+  if (make_tmap(&tmAct, act, dtype, C, M, C, skinny::RP_BK, skinny::RP_BM, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj act")) return 1;
+  if (make_tmap(&tmP, P, dtype, C, rp, C, skinny::RP_BK, rp, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj P")) return 1;
+  skinny::RowProjParams rp_p;
+  rp_p.out = out;
+  rp_p.keep_out = keep_out;
+  rp_p.M = (int)M;
+  rp_p.C = (int)C;
+  rp_p.out_scale = out_scale;
+  rp_p.dropout = p > 0.f ? 1 : 0;
+  rp_p.seed = seed;
+  rp_p.offset = offset;
+  rp_p.thresh16 = static_cast<uint32_t>(p * 65536.0f + 0.5f);
+  const bool bf = dtype == kDtypeBf16;
+#define RP_CASE(BF, RP) return launch_rowproj_t<BF, RP>(tmAct, tmP, rp_p, stream);
+  if (bf) {
+    if (rp == 16) RP_CASE(true, 16) else if (rp == 32) RP_CASE(true, 32) else RP_CASE(true, 64)
+  } else {
+    if (rp == 16) RP_CASE(false, 16) else if (rp == 32) RP_CASE(false, 32) else RP_CASE(false, 64)
+  }
+#undef RP_CASE
+}
+
+template <bool BF, int RP>
+int launch_colproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmSmall, const skinny::ColProjParams& p, int splits,
+                     cudaStream_t stream) {
+  dim3 grid((p.C + skinny::CP_BC - 1) / skinny::CP_BC, splits);
+  skinny::colproj_kernel<BF, RP><<<grid, skinny::CP_THREADS, skinny::cp_smem_bytes<RP>(), stream>>>(tmAct, tmSmall, p);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// out[c*ld_c + j*ld_j] (=|+=) scale * sum_m keep(m,c) act[m,c] small[m,j],  c < C, j < r
+int launch_colproj(const void* act, const void* small, const uint8_t* keep, float* partial, float* out, int64_t M,
+                   int64_t C, int r, int rp, int dtype, long long ld_c, long long ld_j, float scale, int accumulate,
+                   cudaStream_t stream) {
+  CUtensorMap tmAct, tmSmall;
+  if (make_tmap(&tmAct, act, dtype, C, M, C, skinny::CP_BC, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_128B, "colproj act")) return 1;
+  if (make_tmap(&tmSmall, small, dtype, rp, M, rp, rp, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_NONE, "colproj small")) return 1;
+  const Split sp = colproj_split(M, C);
+  skinny::ColProjParams cp;
+  cp.partial = partial;
+  cp.keep = keep;
+  cp.M = (int)M;
+  cp.C = (int)C;
+  cp.rows_per_split = sp.rows_per_split;
+  const bool bf = dtype == kDtypeBf16;
+  int rc;
+#define CP_CASE(BF, RP) rc = launch_colproj_t<BF, RP>(tmAct, tmSmall, cp, sp.splits, stream);
+  if (bf) {
+    if (rp == 16) CP_CASE(true, 16) else if (rp == 32) CP_CASE(true, 32) else CP_CASE(true, 64)
+  } else {
+    if (rp == 16) CP_CASE(false, 16) else if (rp == 32) CP_CASE(false, 32) else CP_CASE(false, 64)
+  }
+#undef CP_CASE
+  if (rc) return rc;
+  const long long total = static_cast<long long>(C) * r;
+  const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, 1024));
+  skinny::reduce_partials_kernel<<<grid, 256, 0, stream>>>(partial, out, sp.splits, (int)C, rp, r, ld_c, ld_j, scale,
+                                                           accumulate);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+struct GemmArgs {
+  const void* A1;  // [M, K1]
+  const void* B1;  // [N, K1] or [K1, N]
+  int b_mn_major;
+  const void* A2;  // [M, rp] or null
+  const void* B2;  // [N, rp] or null
+  int rp;
+  void* D;  // [M, N]
+  const void* bias;
+  int masked_r;
+  const void* dh;
+  const void* a16;
+  const uint8_t* keep;
+  float inv_keep;
+};
+
+int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, int sm_count, cudaStream_t stream) {
+  CUtensorMap tmA1, tmB1, tmA2, tmB2, tmD;
+  if (make_tmap(&tmA1, g.A1, dtype, K1, M, K1, gemm::BK, gemm::BM, CU_TENSOR_MAP_SWIZZLE_128B, "gemm A1")) return 1;
+  if (!g.b_mn_major) {
+    if (make_tmap(&tmB1, g.B1, dtype, K1, N, K1, gemm::BK, gemm::BN, CU_TENSOR_MAP_SWIZZLE_128B, "gemm B1 (K-major)")) return 1;
+  } else {
+    if (make_tmap(&tmB1, g.B1, dtype, N, K1, N, 64, gemm::BK, CU_TENSOR_MAP_SWIZZLE_128B, "gemm B1 (MN-major)")) return 1;
+  }
+  if (g.rp > 0) {
+    const CUtensorMapSwizzle sw = swizzle_for_row_bytes(g.rp * 2);
+    if (make_tmap(&tmA2, g.A2, dtype, g.rp, M, g.rp, g.rp, gemm::BM, sw, "gemm A2")) return 1;
+    if (make_tmap(&tmB2, g.B2, dtype, g.rp, N, g.rp, g.rp, gemm::BN, sw, "gemm B2")) return 1;
+  } else {
+    tmA2 = tmA1;
+    tmB2 = tmB1;
+  }
+  if (make_tmap(&tmD, g.D, dtype, N, M, N, 64, 32, CU_TENSOR_MAP_SWIZZLE_128B, "gemm D")) return 1;
+
+  gemm::Params p;
+  p.M = (int)M;
+  p.N = (int)N;
+  p.K1 = (int)K1;
+  p.r_pad = g.rp;
+  p.b_mn_major = g.b_mn_major;
+  p.dtype = dtype;
+  p.bias = g.bias;
+  p.masked_r = g.masked_r;
+  p.dh = g.dh;
+  p.dh_ld = g.rp > 0 ? g.rp : rpad_of(g.masked_r > 0 ? g.masked_r : 1);
+  p.a16 = g.a16;
+  p.keep = g.keep;
+  p.inv_keep = g.inv_keep;
+
+  const long long tiles = ((M + gemm::BM - 1) / gemm::BM) * ((N + gemm::BN - 1) / gemm::BN);
+  const int grid = static_cast<int>(std::min<long long>(tiles, sm_count));
+  gemm::gemm_lora_kernel<<<grid, gemm::THREADS, gemm::SMEM_BYTES, stream>>>(tmA1, tmB1, tmA2, tmB2, tmD, p);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+__global__ void keep_mask_kernel(uint8_t* keep, long long groups, uint64_t seed, uint64_t offset, uint32_t thresh16) {
+  for (long long g = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; g < groups;
+       g += static_cast<long long>(gridDim.x) * blockDim.x)
+    keep[g] = static_cast<uint8_t>(lb::dropout_keep_bits(static_cast<uint64_t>(g), seed, offset, thresh16));
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* lora_last_error(void) { return g_err.c_str(); }
+
+int32_t lora_linear_rpad(int32_t r) { return rpad_of(r); }
+
+size_t lora_linear_workspace_bytes(int64_t M, int64_t K, int64_t N, int32_t r) {
+  if (M <= 0 || K <= 0 || N <= 0 || r < 1 || r > 64) return 0;
+  return carve(M, K, N, r).total;
+}
+
+int lora_linear_fwd(const void* X, const void* W, const void* bias, const float* A, const float* B, void* Y, void* H,
+                    uint8_t* keep_mask, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p,
+                    uint64_t seed, uint64_t offset, int32_t dtype, int32_t w_is_KN, void* workspace,
+                    size_t workspace_bytes, cudaStream_t stream) {
+  g_err.clear();
+  if (check_common(M, K, N, r, dtype)) return 1;
+  if (!X || !W || !A || !B || !Y || !H || !workspace) return fail("lora_linear_fwd: null pointer argument");
+  if (!(p >= 0.f && p < 1.f)) return fail("dropout p must be in [0,1); got %f", (double)p);
+  if (p > 0.f && !keep_mask) return fail("lora_linear_fwd: keep_mask is required when p > 0");
+  const Workspace w = carve(M, K, N, r);
+  if (workspace_bytes < w.total) return fail("workspace too small: need %zu bytes, got %zu", w.total, workspace_bytes);
+  int sms = 0;
+  if (device_setup(&sms)) return 1;
+  uint8_t* ws = static_cast<uint8_t*>(workspace);
+  const int rp = rpad_of(r);
+  const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
+
+  if (launch_pack(A, B, ws, w, K, N, r, scaling, dtype, stream)) return 1;
+  if (launch_rowproj(X, ws + w.a16, H, keep_mask, M, K, rp, dtype, inv_keep, p, seed, offset, stream)) return 1;
+  GemmArgs g{};
+  g.A1 = X;
+  g.B1 = W;
+  g.b_mn_major = w_is_KN ? 1 : 0;
+  g.A2 = H;
+  g.B2 = ws + w.sb16;
+  g.rp = rp;
+  g.D = Y;
+  g.bias = bias;
+  g.inv_keep = 1.f;
+  return launch_gemm(g, M, N, K, dtype, sms, stream);
+}
+
+int lora_linear_bwd(const void* dY, const void* X, const void* W, const float* A, const float* B, const void* H,
+                    const uint8_t* keep_mask, void* dX, float* dA, float* dB, int64_t M, int64_t K, int64_t N,
+                    int32_t r, float scaling, float p, int32_t dtype, int32_t w_is_KN, int32_t accumulate,
+                    void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+  g_err.clear();
+  if (check_common(M, K, N, r, dtype)) return 1;
+  if (!dY || !X || !W || !A || !B || !H || !dA || !dB || !workspace) return fail("lora_linear_bwd: null pointer argument");
+  if (!(p >= 0.f && p < 1.f)) return fail("dropout p must be in [0,1); got %f", (double)p);
+  if (p > 0.f && !keep_mask) return fail("lora_linear_bwd: keep_mask is required when p > 0");
+  const Workspace w = carve(M, K, N, r);
+  if (workspace_bytes < w.total) return fail("workspace too small: need %zu bytes, got %zu", w.total, workspace_bytes);
+  int sms = 0;
+  if (device_setup(&sms)) return 1;
+  uint8_t* ws = static_cast<uint8_t*>(workspace);
+  const int rp = rpad_of(r);
+  const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  const uint8_t* keep = p > 0.f ? keep_mask : nullptr;
+  void* dH = ws + w.dh;
+  float* partial = reinterpret_cast<float*>(ws + w.partial);
+
+  if (launch_pack(A, B, ws, w, K, N, r, scaling, dtype, stream)) return 1;
+  // dH[M, rp] = dY (sB)
+  if (launch_rowproj(dY, ws + w.sb16t, dH, nullptr, M, N, rp, dtype, 1.f, 0.f, 0, 0, stream)) return 1;
+  if (dX) {
+    GemmArgs g{};
+    g.A1 = dY;
+    g.B1 = W;
+    g.b_mn_major = w_is_KN ? 0 : 1;  // contraction runs over N here
+    g.D = dX;
+    g.inv_keep = inv_keep;
+    if (keep) {
+      g.rp = 0;
+      g.masked_r = r;
+      g.dh = dH;
+      g.a16 = ws + w.a16;
+      g.keep = keep;
+    } else {
+      g.A2 = dH;
+      g.B2 = ws + w.a16t;
+      g.rp = rp;
+    }
+    if (launch_gemm(g, M, K, N, dtype, sms, stream)) return 1;
+    // launch_gemm derives dh_ld from rp/masked_r; both give rp here.
+  }
+  // dB[N, r] = s * dY^T H      (H already carries 1/(1-p))
+  if (launch_colproj(dY, H, nullptr, partial, dB, M, N, r, rp, dtype, r, 1, scaling, accumulate, stream)) return 1;
+  // dA[r, K] = dH^T drop(X)
+  if (launch_colproj(X, dH, keep, partial, dA, M, K, r, rp, dtype, 1, K, inv_keep, accumulate, stream)) return 1;
+  return 0;
+}
+
+int lora_linear_base(const void* X, const void* W, const void* bias, void* Y, int64_t M, int64_t K, int64_t N,
+                     int32_t dtype, int32_t w_is_KN, cudaStream_t stream) {
+  g_err.clear();
+  if (check_common(M, K, N, 1, dtype)) return 1;
+  if (!X || !W || !Y) return fail("lora_linear_base: null pointer argument");
+  int sms = 0;
+  if (device_setup(&sms)) return 1;
+  GemmArgs g{};
+  g.A1 = X;
+  g.B1 = W;
+  g.b_mn_major = w_is_KN ? 1 : 0;
+  g.D = Y;
+  g.bias = bias;
+  g.inv_keep = 1.f;
+  return launch_gemm(g, M, N, K, dtype, sms, stream);
+}
+
+int lora_dropout_keep_mask(uint8_t* keep_mask, int64_t M, int64_t K, float p, uint64_t seed, uint64_t offset,
+                           cudaStream_t stream) {
+  g_err.clear();
+  if (!keep_mask) return fail("lora_dropout_keep_mask: null pointer argument");
+  if (M <= 0 || K <= 0 || K % 8 != 0) return fail("lora_dropout_keep_mask: need M > 0, K > 0, K %% 8 == 0");
+  if (!(p >= 0.f && p < 1.f)) return fail("dropout p must be in [0,1); got %f", (double)p);
+  const long long groups = static_cast<long long>(M) * (K / 8);
+  const int grid = static_cast<int>(std::min<long long>((groups + 255) / 256, 4096));
+  keep_mask_kernel<<<grid, 256, 0, stream>>>(keep_mask, groups, seed, offset, static_cast<uint32_t>(p * 65536.0f + 0.5f));
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

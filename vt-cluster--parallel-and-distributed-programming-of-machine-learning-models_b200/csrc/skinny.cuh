@@ -1,0 +1,430 @@
+// HBM-bound companions of the tcgen05 GEMM: everything whose arithmetic
+// intensity is ~r flop/byte: the rank-r projections
+//     H  = drop(X) A^T          dH = dY (sB)            (rowproj)
+//     dB = s dY^T H             dA = dH^T drop(X)       (colproj + reduce)
+// plus the fp32 -> 16-bit adapter packing.  They stream the activation once
+// through a TMA + mbarrier ring and use warp-level mma.sync on the tiles:
+// the tensor pipe is nowhere near the limit here, HBM is.
+//
+// Follows peft lora.Linear semantics as used at
+// finetune_lora_distilgpt2.py:98-104 / finetune_lora_opt_pp.py:104-112:
+// dropout acts on the adapter input only, scaling = lora_alpha / r.
+#pragma once
+
+#include "common.cuh"
+
+namespace lb {
+namespace skinny {
+
+// ---------------------------------------------------------------------------
+// mma.sync / ldmatrix wrappers
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x2(uint32_t addr, uint32_t (&r)[2]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x2.shared.b16 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x2_t(uint32_t addr, uint32_t (&r)[2]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0,%1}, [%2];"
+               : "=r"(r[0]), "=r"(r[1])
+               : "r"(addr));
+}
+template <bool kBf16>
+__device__ __forceinline__ void mma_16816(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+  if constexpr (kBf16) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+  } else {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+  }
+}
+// Zero the 16-bit lanes of a 16-byte chunk whose keep-bit is clear.
+__device__ __forceinline__ uint4 apply_keep(uint4 x, uint32_t bits) {
+  uint32_t w[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const uint32_t lo = (bits >> (2 * e)) & 1u, hi = (bits >> (2 * e + 1)) & 1u;
+    w[e] &= (lo ? 0x0000FFFFu : 0u) | (hi ? 0xFFFF0000u : 0u);
+  }
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+// ---------------------------------------------------------------------------
+// pack: fp32 masters A[r,K], B[N,r] -> 16-bit operands in the four layouts the
+// kernels read (zero padded to r_pad; the scaling s is folded into B).
+//   a16 [r_pad,K]   a16t [K,r_pad]   sb16 [N,r_pad]   sb16t [r_pad,N]
+// ---------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ T cvt16(float v);
+template <>
+__device__ __forceinline__ __nv_bfloat16 cvt16<__nv_bfloat16>(float v) {
+  return __float2bfloat16_rn(v);
+}
+template <>
+__device__ __forceinline__ __half cvt16<__half>(float v) {
+  return __float2half_rn(v);
+}
+
+template <typename T>
+__global__ void pack_adapters_kernel(const float* __restrict__ A, const float* __restrict__ B, T* __restrict__ a16,
+                                     T* __restrict__ a16t, T* __restrict__ sb16, T* __restrict__ sb16t, int K, int N,
+                                     int r, int r_pad, float s) {
+  const long long na = static_cast<long long>(r_pad) * K;
+  const long long nb = static_cast<long long>(N) * r_pad;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < na + nb;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    if (i < na) {
+      const int j = static_cast<int>(i / K), k = static_cast<int>(i % K);
+      const T v = cvt16<T>(j < r ? A[static_cast<long long>(j) * K + k] : 0.f);
+      a16[i] = v;
+      a16t[static_cast<long long>(k) * r_pad + j] = v;
+    } else {
+      const long long t = i - na;
+      const int n = static_cast<int>(t / r_pad), j = static_cast<int>(t % r_pad);
+      const T v = cvt16<T>(j < r ? s * B[static_cast<long long>(n) * r + j] : 0.f);
+      sb16[t] = v;
+      sb16t[static_cast<long long>(j) * N + n] = v;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// rowproj: Out[M, kRPad] = out_scale * (keep .* Act)[M, C] * P[kRPad, C]^T
+// One CTA per 64 rows; warp 4 is the TMA producer, warps 0..3 own 16 rows each.
+// With dropout on, each warp first zeroes the dropped elements of its own rows
+// in shared memory (one Philox call per 8 elements) and publishes the keep-bits.
+// ---------------------------------------------------------------------------
+constexpr int RP_BM = 64;
+constexpr int RP_BK = 64;
+constexpr int RP_STAGES = 6;
+constexpr int RP_ACT_BYTES = RP_BM * 128;  // 8 KiB
+constexpr int RP_CONSUMERS = 4;
+constexpr int RP_THREADS = (RP_CONSUMERS + 1) * 32;
+template <int kRPad>
+__host__ __device__ constexpr int rp_slot_bytes() {
+  return RP_ACT_BYTES + ((kRPad * 128 + 1023) / 1024) * 1024;
+}
+template <int kRPad>
+__host__ __device__ constexpr int rp_smem_bytes() {
+  return RP_STAGES * rp_slot_bytes<kRPad>() + 1024 + 256;
+}
+
+struct RowProjParams {
+  void* out;  // [M, kRPad] 16-bit
+  uint8_t* keep_out;  // [M, C/8] or null
+  int M, C;
+  float out_scale;
+  int dropout;  // 0/1
+  uint64_t seed, offset;
+  uint32_t thresh16;
+};
+
+template <bool kBf16, int kRPad>
+__global__ void __launch_bounds__(RP_THREADS)
+    rowproj_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constant__ CUtensorMap tmP,
+                   const RowProjParams p) {
+  constexpr int SLOT = rp_slot_bytes<kRPad>();
+  constexpr int NB = kRPad / 8;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + RP_STAGES * SLOT);
+  uint64_t* empty = full + RP_STAGES;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * RP_BM;
+  const int nk = (p.C + RP_BK - 1) / RP_BK;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < RP_STAGES; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], RP_CONSUMERS);
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+
+  if (warp == RP_CONSUMERS) {
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int kb = 0; kb < nk; ++kb) {
+        mbar_wait(&empty[stage], phase ^ 1, 11);
+        uint8_t* act = smem + stage * SLOT;
+        mbar_arrive_expect_tx(&full[stage], RP_ACT_BYTES + kRPad * 128);
+        tma_load_2d(act, &tmAct, &full[stage], kb * RP_BK, m0);
+        tma_load_2d(act + RP_ACT_BYTES, &tmP, &full[stage], kb * RP_BK, 0);
+        if (++stage == RP_STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+    __syncwarp();
+    return;
+  }
+
+  float acc[NB][4];
+#pragma unroll
+  for (int n = 0; n < NB; ++n)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) acc[n][e] = 0.f;
+
+  const int keep_ld = p.C >> 3;
+  uint32_t stage = 0, phase = 0;
+  for (int kb = 0; kb < nk; ++kb) {
+    mbar_wait(&full[stage], phase, 12);
+    uint8_t* act = smem + stage * SLOT;
+    uint8_t* pt = act + RP_ACT_BYTES;
+    if (p.dropout) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int idx = lane + 32 * i;
+        const int R = warp * 16 + (idx >> 3), ch = idx & 7;
+        const int m = m0 + R, c = kb * RP_BK + ch * 8;
+        if (m < p.M && c < p.C) {
+          const uint64_t g = (static_cast<uint64_t>(m) * static_cast<uint64_t>(p.C) + static_cast<uint64_t>(c)) >> 3;
+          const uint32_t bits = dropout_keep_bits(g, p.seed, p.offset, p.thresh16);
+          uint4* ptr = reinterpret_cast<uint4*>(act + R * 128 + ((ch ^ (R & 7)) << 4));
+          *ptr = apply_keep(*ptr, bits);
+          p.keep_out[static_cast<size_t>(m) * keep_ld + (c >> 3)] = static_cast<uint8_t>(bits);
+        }
+      }
+      __syncwarp();
+    }
+    const uint32_t act_u = smem_u32(act), pt_u = smem_u32(pt);
+#pragma unroll
+    for (int ks = 0; ks < RP_BK / 16; ++ks) {
+      uint32_t a[4];
+      {
+        const int R = warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+        const int ch = ks * 2 + (lane >> 4);
+        ldsm_x4(act_u + R * 128 + ((ch ^ (R & 7)) << 4), a);
+      }
+#pragma unroll
+      for (int n = 0; n < NB; ++n) {
+        uint32_t b[2];
+        const int prow = n * 8 + (lane & 7);
+        const int ch = ks * 2 + ((lane >> 3) & 1);
+        ldsm_x2(pt_u + prow * 128 + ((ch ^ (prow & 7)) << 4), b);
+        mma_16816<kBf16>(acc[n], a, b);
+      }
+    }
+    if (p.dropout) fence_proxy_async_smem();  // our in-place writes precede the next TMA overwrite
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[stage]);
+    if (++stage == RP_STAGES) {
+      stage = 0;
+      phase ^= 1;
+    }
+  }
+
+  // acc fragment: (row = lane/4 [+8], col = n*8 + (lane%4)*2 [+1])
+  uint32_t* out = reinterpret_cast<uint32_t*>(p.out);
+  const int r0 = m0 + warp * 16 + (lane >> 2);
+#pragma unroll
+  for (int n = 0; n < NB; ++n) {
+    const int col = n * 8 + (lane & 3) * 2;
+    if (r0 < p.M)
+      out[(static_cast<size_t>(r0) * kRPad + col) >> 1] =
+          pack2(acc[n][0] * p.out_scale, acc[n][1] * p.out_scale, kBf16 ? kDtypeBf16 : kDtypeFp16);
+    if (r0 + 8 < p.M)
+      out[(static_cast<size_t>(r0 + 8) * kRPad + col) >> 1] =
+          pack2(acc[n][2] * p.out_scale, acc[n][3] * p.out_scale, kBf16 ? kDtypeBf16 : kDtypeFp16);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// colproj: partial[split][C, kRPad] = sum over the split's rows m of
+//          (keep .* Act)[m, c] * Small[m, j]        (fp32)
+// grid = (ceil(C/64), splits).  Warp 8 is the TMA producer; consumer warp w
+// owns rows 16w..16w+15 of every 128-row tile and all 64 columns; partial sums
+// of the 8 warps meet in shared memory, splits meet in reduce_partials_kernel.
+// ---------------------------------------------------------------------------
+constexpr int CP_BM = 128;
+constexpr int CP_BC = 64;
+constexpr int CP_STAGES = 4;
+constexpr int CP_ACT_BYTES = CP_BM * 128;  // 16 KiB
+constexpr int CP_CONSUMERS = 8;
+constexpr int CP_THREADS = (CP_CONSUMERS + 1) * 32;
+template <int kRPad>
+__host__ __device__ constexpr int cp_slot_bytes() {
+  return CP_ACT_BYTES + ((CP_BM * kRPad * 2 + 1023) / 1024) * 1024;
+}
+template <int kRPad>
+__host__ __device__ constexpr int cp_smem_bytes() {
+  return CP_STAGES * cp_slot_bytes<kRPad>() + CP_BC * kRPad * 4 + 1024 + 256;
+}
+
+struct ColProjParams {
+  float* partial;       // [splits][C][kRPad]
+  const uint8_t* keep;  // [M, C/8] or null
+  int M, C;
+  int rows_per_split;  // multiple of CP_BM
+};
+
+template <bool kBf16, int kRPad>
+__global__ void __launch_bounds__(CP_THREADS)
+    colproj_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constant__ CUtensorMap tmSmall,
+                   const ColProjParams p) {
+  constexpr int SLOT = cp_slot_bytes<kRPad>();
+  constexpr int NB = kRPad / 8;
+  constexpr int SROW = kRPad * 2;  // bytes per row of the Small tile
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  float* sout = reinterpret_cast<float*>(smem + CP_STAGES * SLOT);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + CP_STAGES * SLOT + CP_BC * kRPad * 4);
+  uint64_t* empty = full + CP_STAGES;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int c0 = blockIdx.x * CP_BC;
+  const int m_begin = blockIdx.y * p.rows_per_split;
+  const int m_end = min(p.M, m_begin + p.rows_per_split);
+  const int nt = (m_end > m_begin) ? (m_end - m_begin + CP_BM - 1) / CP_BM : 0;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < CP_STAGES; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], CP_CONSUMERS);
+    }
+    fence_barrier_init();
+  }
+  for (int i = threadIdx.x; i < CP_BC * kRPad; i += CP_THREADS) sout[i] = 0.f;
+  __syncthreads();
+
+  if (warp == CP_CONSUMERS) {
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int t = 0; t < nt; ++t) {
+        mbar_wait(&empty[stage], phase ^ 1, 21);
+        uint8_t* act = smem + stage * SLOT;
+        mbar_arrive_expect_tx(&full[stage], CP_ACT_BYTES + CP_BM * SROW);
+        tma_load_2d(act, &tmAct, &full[stage], c0, m_begin + t * CP_BM);
+        tma_load_2d(act + CP_ACT_BYTES, &tmSmall, &full[stage], 0, m_begin + t * CP_BM);
+        if (++stage == CP_STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    float acc[4][NB][4];
+#pragma unroll
+    for (int cbk = 0; cbk < 4; ++cbk)
+#pragma unroll
+      for (int n = 0; n < NB; ++n)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) acc[cbk][n][e] = 0.f;
+
+    const int keep_ld = p.C >> 3;
+    uint32_t stage = 0, phase = 0;
+    for (int t = 0; t < nt; ++t) {
+      mbar_wait(&full[stage], phase, 22);
+      uint8_t* act = smem + stage * SLOT;
+      const int mt = m_begin + t * CP_BM;
+      if (p.keep != nullptr) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int idx = lane + 32 * i;
+          const int R = warp * 16 + (idx >> 3), ch = idx & 7;
+          const int m = mt + R, c = c0 + ch * 8;
+          if (m < p.M && c < p.C) {
+            const uint32_t bits = __ldg(p.keep + static_cast<size_t>(m) * keep_ld + (c >> 3));
+            uint4* ptr = reinterpret_cast<uint4*>(act + R * 128 + ((ch ^ (R & 7)) << 4));
+            *ptr = apply_keep(*ptr, bits);
+          }
+        }
+        __syncwarp();
+      }
+      // Rows of the last tile of a split that belong to the next split (or lie
+      // beyond M, where TMA filled zeros) must not contribute.
+      const int valid_rows = m_end - mt;  // > 0
+      const uint32_t act_u = smem_u32(act), sm_u = act_u + CP_ACT_BYTES;
+      const bool warp_live = warp * 16 < valid_rows;
+      if (warp_live) {
+        uint32_t b[NB][2];
+#pragma unroll
+        for (int n = 0; n < NB; ++n) {
+          const int mrow = warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+          ldsm_x2_t(sm_u + mrow * SROW + n * 16, b[n]);
+        }
+        if (warp * 16 + 16 > valid_rows) {
+          // Partially valid 16-row slab: zero B-fragment entries of dead rows.
+          // b[n][0] holds k = (lane%4)*2 + {0,1}, b[n][1] holds k + 8.
+#pragma unroll
+          for (int n = 0; n < NB; ++n)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const int k = warp * 16 + h * 8 + (lane & 3) * 2;
+              uint32_t msk = 0;
+              if (k < valid_rows) msk |= 0x0000FFFFu;
+              if (k + 1 < valid_rows) msk |= 0xFFFF0000u;
+              b[n][h] &= msk;
+            }
+        }
+#pragma unroll
+        for (int cbk = 0; cbk < 4; ++cbk) {
+          uint32_t a[4];
+          const int q = lane >> 3, i = lane & 7;
+          const int mrow = warp * 16 + (q >> 1) * 8 + i;
+          const int ch = cbk * 2 + (q & 1);
+          ldsm_x4_t(act_u + mrow * 128 + ((ch ^ (mrow & 7)) << 4), a);
+#pragma unroll
+          for (int n = 0; n < NB; ++n) mma_16816<kBf16>(acc[cbk][n], a, b[n]);
+        }
+      }
+      if (p.keep != nullptr) fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[stage]);
+      if (++stage == CP_STAGES) {
+        stage = 0;
+        phase ^= 1;
+      }
+    }
+    // acc fragment: (row c = cbk*16 + lane/4 [+8], col j = n*8 + (lane%4)*2 [+1])
+#pragma unroll
+    for (int cbk = 0; cbk < 4; ++cbk)
+#pragma unroll
+      for (int n = 0; n < NB; ++n)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int c = cbk * 16 + (lane >> 2) + ((e >> 1) ? 8 : 0);
+          const int j = n * 8 + (lane & 3) * 2 + (e & 1);
+          atomicAdd(&sout[c * kRPad + j], acc[cbk][n][e]);
+        }
+  }
+  __syncthreads();
+  float* dst = p.partial + (static_cast<size_t>(blockIdx.y) * p.C + c0) * kRPad;
+  const int ncols = min(CP_BC, p.C - c0);
+  for (int i = threadIdx.x; i < ncols * kRPad; i += CP_THREADS) dst[i] = sout[i];
+}
+
+// out[c*ld_c + j*ld_j] = scale * sum_split partial[split][c][j]  (+ old if accumulate), j < r
+__global__ void reduce_partials_kernel(const float* __restrict__ partial, float* __restrict__ out, int splits, int C,
+                                       int r_pad, int r, long long ld_c, long long ld_j, float scale,
+                                       int accumulate) {
+  const long long total = static_cast<long long>(C) * r;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i / r), j = static_cast<int>(i % r);
+    float s = 0.f;
+    for (int sp = 0; sp < splits; ++sp) s += partial[(static_cast<size_t>(sp) * C + c) * r_pad + j];
+    float* o = out + c * ld_c + j * ld_j;
+    *o = accumulate ? (*o + scale * s) : (scale * s);
+  }
+}
+
+}  // namespace skinny
+}  // namespace lb
