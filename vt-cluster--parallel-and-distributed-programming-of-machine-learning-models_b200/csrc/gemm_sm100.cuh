@@ -232,7 +232,8 @@ __global__ void __launch_bounds__(THREADS, 1)
       mbar_wait(&tmem_full[buf], acc_phase, 4);
       tc_fence_after();
 
-      for (int cb = 0; cb < BN / 64; ++cb) {
+      const bool warp_rows_ok = m_blk * BM + ew * 32 < p.M;  // else this warp's 32 rows are all padding
+      for (int cb = 0; cb < BN / 64 && warp_rows_ok; ++cb) {
         const int col0 = n_blk * BN + cb * 64;
         if (col0 >= p.N) break;  // warp-uniform
         if (lane == 0) bulk_wait_group_read<1>();  // the buffer we are about to overwrite has been read
