@@ -1,0 +1,361 @@
+#!/usr/bin/env python
+"""Benchmark of the fused LoRA-linear hot path (BASELINE.json configs[1]).
+
+A step = one forward + one backward of ONE LoRA-adapted projection over a batch of M synthetic
+tokens (OPT-2.7B q_proj shape by default: 2560 -> 2560, r=8, lora_alpha=16, dropout 0.05, bf16).
+`value` is tokens/s with inputs resident in HBM; `e2e` runs the same step through the public
+autograd API with pinned HOST buffers (H2D of X and dY, D2H of Y, dX, dA, dB inside the timed
+region); `roofline` is the tcgen05 GEMM kernel timed alone, live, with CUDA events;
+`cpu_baseline` is the CPU oracle (torch fp32, the reference's engine) on a bounded sample.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    torchrun --nproc-per-node N bench.py --gpus N ...      (one rank per GPU, NCCL)
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import torch
+
+REPO_ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO_ROOT)
+
+METRIC = "lora_linear_fwd_bwd_tokens_per_sec"
+UNIT = "tokens/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--tokens", type=int, default=16384, help="M: tokens per step per GPU")
+    ap.add_argument("--k", type=int, default=2560)
+    ap.add_argument("--n", type=int, default=2560)
+    ap.add_argument("--r", type=int, default=8)
+    ap.add_argument("--p", type=float, default=0.05)
+    ap.add_argument("--dtype", choices=["bf16", "fp16"], default="bf16")
+    ap.add_argument("--conv1d", action="store_true", help="GPT-2 Conv1D weight layout [K,N]")
+    ap.add_argument("--cpu-tokens", type=int, default=2048, help="tokens per step of the CPU legs (bounded sample)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sweep", action="store_true", help="run the configs[1] shape sweep, one JSON line per point")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return (f"configs[1] fused LoRA-linear microbench point: fwd+bwd, {a.k}->{a.n} "
+            f"({'Conv1D [K,N]' if a.conv1d else 'nn.Linear [N,K]'}), r={a.r}, alpha=16, dropout={a.p}, "
+            f"M={a.tokens} tokens/GPU")
+
+
+def flops_fwd_bwd(M, K, N, r):
+    return 4.0 * M * K * N + 6.0 * M * r * (K + N)
+
+
+def flops_gemm_launch(M, K, N, r):
+    return 2.0 * M * K * N + 2.0 * M * r * N  # frozen GEMM + the rank-r K-block it carries
+
+
+def measured_peaks():
+    path = os.path.join(REPO_ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            d = json.load(f)
+        return float(d["bf16_tflops"]), float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), "measured"
+    return 1590.0, 1400.0, "fallback"
+
+
+class ClockSampler:
+    """Samples SM clock / throttle reasons through NVML while the timed region runs."""
+
+    REASONS = {0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown",
+               0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                mask = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._t is not None:
+            self._t.join()
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def make_inputs(a, M, device, dtype, seed):
+    g = torch.Generator().manual_seed(seed)
+    K, N, r = a.k, a.n, a.r
+    x = torch.randn(M, K, generator=g)
+    W = torch.randn((K, N) if a.conv1d else (N, K), generator=g) * 0.02
+    b = torch.randn(N, generator=g) * 0.02
+    A = (torch.rand(r, K, generator=g) * 2 - 1) / (K ** 0.5)
+    B = torch.randn(N, r, generator=g) * 0.02  # non-zero, else dA == 0 and the low-rank path idles
+    dy = torch.randn(M, N, generator=g)
+    cast = lambda t: t.to(dtype).to(device)
+    return cast(x), cast(W), cast(b), A.to(device), B.to(device), cast(dy)
+
+
+# ----------------------------------------------------------------------------------------------
+# CPU legs (oracle = torch fp32 CPU restatement of peft's LoRA linear; see oracle/lora_ref.py)
+# ----------------------------------------------------------------------------------------------
+def cpu_step_time(a, tokens, steps, warmup):
+    from oracle import lora_ref, philox
+
+    x, W, b, A, B, dy = make_inputs(a, tokens, "cpu", torch.float32, 1234)
+    keep = torch.from_numpy(philox.keep_mask(tokens, a.k, a.p, 1, 0)) if a.p > 0 else None
+    s = 16.0 / a.r
+    for _ in range(warmup):
+        lora_ref.lora_linear_fwd_bwd(x, W, b, A, B, s, dy, keep, a.p, a.conv1d)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        lora_ref.lora_linear_fwd_bwd(x, W, b, A, B, s, dy, keep, a.p, a.conv1d)
+    return (time.perf_counter() - t0) / steps
+
+
+def run_reference(a, rank):
+    """--impl reference: the reference's own CPU implementation of the path.  peft/accelerate/
+    deepspeed cannot be installed here, so this is the oracle port on all host threads."""
+    if rank != 0:
+        return
+    cores = torch.get_num_threads()
+    t = cpu_step_time(a, a.cpu_tokens, a.steps, max(1, min(a.warmup, 3)))
+    v = a.cpu_tokens / t
+    sample = f"{a.cpu_tokens} tokens/step x {a.steps} steps of the same layer shape, torch fp32 CPU"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": {"workload": workload_name(a), "sample": sample},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ----------------------------------------------------------------------------------------------
+# GPU legs
+# ----------------------------------------------------------------------------------------------
+def run_point(a, pkg, rank, world, device, emit=True):
+    bind = pkg.binding
+    dtype = torch.bfloat16 if a.dtype == "bf16" else torch.float16
+    M, K, N, r, p = a.tokens, a.k, a.n, a.r, a.p
+    s = 16.0 / r
+    x, W, b, A, B, dy = make_inputs(a, M, device, dtype, 1234 + rank)
+    ws = torch.empty(bind.workspace_bytes(M, K, N, r), dtype=torch.uint8, device=device)
+    dA = torch.empty(r, K, device=device)
+    dB = torch.empty(N, r, device=device)
+    bucket = torch.empty(r * K + N * r, device=device)  # DDP-style flat adapter-gradient bucket
+    dist_on = world > 1
+    if dist_on:
+        import torch.distributed as dist
+
+    def step(i):
+        Y, H, keep = bind.linear_fwd(x, W, b, A, B, s, p, 1, 4 * i, a.conv1d, ws)
+        bind.linear_bwd(dy, x, W, A, B, H, keep, s, p, a.conv1d, ws, need_dx=True, dA=dA, dB=dB)
+        if dist_on:  # the path's one exchange step under DDP: average the adapter gradients
+            bucket[: r * K].copy_(dA.view(-1))
+            bucket[r * K:].copy_(dB.view(-1))
+            dist.all_reduce(bucket, op=dist.ReduceOp.AVG)
+        return Y
+
+    def barrier():
+        if dist_on:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(a.warmup):
+        step(i)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(torch.cuda.current_device()) as clk:
+        e0.record()
+        for i in range(a.steps):
+            step(i)
+        e1.record()
+        barrier()
+    ms = e0.elapsed_time(e1)
+    if dist_on:
+        t = torch.tensor([ms], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_step = ms / a.steps
+    value = world * M / (ms_step * 1e-3)
+
+    # ---- dominant kernel alone (tcgen05 GEMM of the forward), live, CUDA events on this stream ----
+    try:
+        Y, H, keep = bind.linear_fwd(x, W, b, A, B, s, p, 1, 0, a.conv1d, ws)  # leaves valid packed operands
+        bind.set_phase_mask(bind.PHASE_GEMM)
+        Ybuf = torch.empty_like(Y)
+        n_rep = max(20, a.steps)
+        for _ in range(5):
+            bind.lib().lora_linear_fwd(x.data_ptr(), W.data_ptr(), b.data_ptr(), A.data_ptr(), B.data_ptr(),
+                                       Ybuf.data_ptr(), H.data_ptr(), keep.data_ptr(), M, K, N, r, s, p, 1, 0,
+                                       bind.dtype_code(dtype), int(a.conv1d), ws.data_ptr(), ws.numel(),
+                                       torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        for _ in range(n_rep):
+            bind.lib().lora_linear_fwd(x.data_ptr(), W.data_ptr(), b.data_ptr(), A.data_ptr(), B.data_ptr(),
+                                       Ybuf.data_ptr(), H.data_ptr(), keep.data_ptr(), M, K, N, r, s, p, 1, 0,
+                                       bind.dtype_code(dtype), int(a.conv1d), ws.data_ptr(), ws.numel(),
+                                       torch.cuda.current_stream().cuda_stream)
+        g1.record()
+        torch.cuda.synchronize()
+        gemm_ms = g0.elapsed_time(g1) / n_rep
+    finally:
+        bind.set_phase_mask(bind.PHASE_ALL)
+    burst, sustained, src = measured_peaks()
+    achieved = flops_gemm_launch(M, K, N, r) / (gemm_ms * 1e-3) / 1e12
+    traffic = None
+    tpath = os.path.join(REPO_ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get(f"{M}x{K}x{N}")
+    roofline = {"kernel": "lb::gemm::gemm_lora_kernel (forward launch)", "bound": "tensor", "achieved": achieved,
+                "peak": burst, "unit": "TFLOP/s", "frac": achieved / burst, "traffic": traffic,
+                "peak_source": f"{src} burst bf16 (MEASURED_PEAKS.json)", "kernel_ms": gemm_ms,
+                "step_tflops": flops_fwd_bwd(M, K, N, r) / (ms_step * 1e-3) / 1e12,
+                "step_frac_of_sustained": flops_fwd_bwd(M, K, N, r) / (ms_step * 1e-3) / 1e12 / sustained}
+
+    # ---- e2e: public autograd API, pinned host buffers, copies inside the timed region ----
+    hx = torch.empty(M, K, dtype=dtype).pin_memory().copy_(x.cpu())
+    hdy = torch.empty(M, N, dtype=dtype).pin_memory().copy_(dy.cpu())
+    hy = torch.empty(M, N, dtype=dtype).pin_memory()
+    hdx = torch.empty(M, K, dtype=dtype).pin_memory()
+    hda = torch.empty(r, K).pin_memory()
+    hdb = torch.empty(N, r).pin_memory()
+    Ap, Bp = A.clone().requires_grad_(True), B.clone().requires_grad_(True)
+
+    def e2e_step():
+        xd = hx.to(device, non_blocking=True).requires_grad_(True)
+        dyd = hdy.to(device, non_blocking=True)
+        y = pkg.fused_lora_linear(xd, W, b, Ap, Bp, s, p=p, training=True, w_is_KN=a.conv1d)
+        y.backward(dyd)
+        hy.copy_(y.detach(), non_blocking=True)
+        hdx.copy_(xd.grad, non_blocking=True)
+        hda.copy_(Ap.grad, non_blocking=True)
+        hdb.copy_(Bp.grad, non_blocking=True)
+        Ap.grad = None
+        Bp.grad = None
+
+    e2e_steps = max(5, min(a.steps, 20))
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    e0.record()
+    for _ in range(e2e_steps):
+        e2e_step()
+    e1.record()
+    barrier()
+    e2e_ms = e0.elapsed_time(e1) / e2e_steps
+    if dist_on:
+        t = torch.tensor([e2e_ms], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item())
+    esz = 2
+    e2e = {"value": world * M / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": (M * K + M * N) * esz,
+           "d2h_bytes_per_step": (M * N + M * K) * esz + (r * K + N * r) * 4, "ms_per_step": e2e_ms}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": a.dtype, "data": "synthetic",
+        "config": {"workload": workload_name(a), "M": M, "K": K, "N": N, "r": r, "lora_alpha": 16, "dropout": p,
+                   "w_layout": "KN" if a.conv1d else "NK", "parallelism": f"dp{world}",
+                   "l2_policy": "inputs larger than L2 (X, dY, Y, dX, W = %.0f MB per step vs 126 MB L2)" %
+                                ((3 * M * K + 2 * M * N + K * N) * 2 / 1e6 if K == N else
+                                 (2 * M * K + 2 * M * N + K * N) * 2 / 1e6),
+                   "exchange": "NCCL all-reduce(avg) of the flat adapter-grad bucket per step" if dist_on else "none"},
+        "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 10 * a.steps, "roofline": roofline,
+    }
+    return line
+
+
+def main():
+    a = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if a.impl == "reference":
+        run_reference(a, rank)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the fused LoRA kernels have no CPU fallback "
+                         "(use --impl reference for the CPU reference arm)")
+    import __graft_entry__ as g
+
+    g.build()
+    pkg = g.load_package()
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+    try:
+        if a.sweep:
+            shapes = [(768, 2304, True), (768, 768, True), (3072, 768, True), (2560, 2560, False),
+                      (2560, 10240, False), (10240, 2560, False)]
+            for (K, N, conv) in shapes:
+                for r in (8, 16, 64):
+                    for M in (4096, 16384, 65536):
+                        a.k, a.n, a.conv1d, a.r, a.tokens = K, N, conv, r, M
+                        line = run_point(a, pkg, rank, world, device)
+                        if rank == 0:
+                            print(json.dumps(line), flush=True)
+            return
+        line = run_point(a, pkg, rank, world, device)
+        if rank == 0:
+            if world == 1 and not a.no_cpu_baseline:
+                cores = torch.get_num_threads()
+                t = cpu_step_time(a, a.cpu_tokens, 5, 1)
+                line["cpu_baseline"] = {"value": a.cpu_tokens / t, "unit": UNIT, "cores": cores, "kind": "port",
+                                        "sample": f"{a.cpu_tokens} tokens/step x 5 steps, same layer shape, "
+                                                  "oracle/lora_ref.py (torch fp32 CPU)"}
+            print(json.dumps(line), flush=True)
+    finally:
+        if world > 1:
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

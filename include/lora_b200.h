@@ -93,6 +93,16 @@ int lora_linear_base(const void* X, const void* W, const void* bias, void* Y, in
 int lora_dropout_keep_mask(uint8_t* keep_mask, int64_t M, int64_t K, float p, uint64_t seed, uint64_t offset,
                            cudaStream_t stream);
 
+/*
+ * Profiling hook, no counterpart in the reference: restricts which kernels the
+ * calls above launch (bit 0 adapter packing, bit 1 rank-r row projections
+ * H/dH, bit 2 the tcgen05 GEMM, bit 3 dA/dB column projections + reduce;
+ * default 15 = all).  Process-wide; bench.py uses it to time the dominant
+ * kernel alone on data left in the workspace by a preceding full call.
+ * Results of a masked call are NOT a valid forward/backward.
+ */
+void lora_debug_set_phase_mask(int32_t mask);
+
 #ifdef __cplusplus
 }
 #endif

@@ -34,6 +34,7 @@ _SIGNATURES = {
                            c_size_t, c_void_p],
     ),
     "lora_linear_base": (c_int, [c_void_p] * 4 + [c_int64, c_int64, c_int64, c_int32, c_int32, c_void_p]),
+    "lora_debug_set_phase_mask": (None, [c_int32]),
     "lora_dropout_keep_mask": (c_int, [c_void_p, c_int64, c_int64, c_float, c_uint64, c_uint64, c_void_p]),
 }
 
@@ -144,6 +145,14 @@ def linear_base(x2d, W, bias, w_is_KN):
                                 int(bool(w_is_KN)), _stream())
     _check(rc, "lora_linear_base")
     return Y
+
+
+PHASE_PACK, PHASE_ROWPROJ, PHASE_GEMM, PHASE_COLPROJ, PHASE_ALL = 1, 2, 4, 8, 15
+
+
+def set_phase_mask(mask: int = PHASE_ALL):
+    """Profiling only (see include/lora_b200.h): choose which kernels fwd/bwd launch."""
+    lib().lora_debug_set_phase_mask(int(mask))
 
 
 def dropout_keep_mask(M, K, p, seed, offset, device="cuda"):

@@ -73,6 +73,11 @@ CUtensorMapSwizzle swizzle_for_row_bytes(int bytes) {
   return bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : (bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
+// Profiling hook (lora_debug_set_phase_mask): which kernels a call launches.
+enum : int { kPhasePack = 1, kPhaseRowProj = 2, kPhaseGemm = 4, kPhaseColProj = 8, kPhaseAll = 15 };
+std::atomic<int> g_phase_mask{kPhaseAll};
+inline bool phase_on(int ph) { return (g_phase_mask.load(std::memory_order_relaxed) & ph) != 0; }
+
 constexpr int kMaxDevices = 64;
 struct DeviceInfo {
   std::atomic<int> ready{0};
@@ -345,8 +350,11 @@ int lora_linear_fwd(const void* X, const void* W, const void* bias, const float*
   const int rp = rpad_of(r);
   const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
 
-  if (launch_pack(A, B, ws, w, K, N, r, scaling, dtype, stream)) return 1;
-  if (launch_rowproj(X, ws + w.a16, H, keep_mask, M, K, rp, dtype, inv_keep, p, seed, offset, stream)) return 1;
+  if (phase_on(kPhasePack) && launch_pack(A, B, ws, w, K, N, r, scaling, dtype, stream)) return 1;
+  if (phase_on(kPhaseRowProj) &&
+      launch_rowproj(X, ws + w.a16, H, keep_mask, M, K, rp, dtype, inv_keep, p, seed, offset, stream))
+    return 1;
+  if (!phase_on(kPhaseGemm)) return 0;
   GemmArgs g{};
   g.A1 = X;
   g.B1 = W;
@@ -380,10 +388,11 @@ int lora_linear_bwd(const void* dY, const void* X, const void* W, const float* A
   void* dH = ws + w.dh;
   float* partial = reinterpret_cast<float*>(ws + w.partial);
 
-  if (launch_pack(A, B, ws, w, K, N, r, scaling, dtype, stream)) return 1;
+  if (phase_on(kPhasePack) && launch_pack(A, B, ws, w, K, N, r, scaling, dtype, stream)) return 1;
   // dH[M, rp] = dY (sB)
-  if (launch_rowproj(dY, ws + w.sb16t, dH, nullptr, M, N, rp, dtype, 1.f, 0.f, 0, 0, stream)) return 1;
-  if (dX) {
+  if (phase_on(kPhaseRowProj) && launch_rowproj(dY, ws + w.sb16t, dH, nullptr, M, N, rp, dtype, 1.f, 0.f, 0, 0, stream))
+    return 1;
+  if (dX && phase_on(kPhaseGemm)) {
     GemmArgs g{};
     g.A1 = dY;
     g.B1 = W;
@@ -404,6 +413,7 @@ int lora_linear_bwd(const void* dY, const void* X, const void* W, const float* A
     if (launch_gemm(g, M, K, N, dtype, sms, stream)) return 1;
     // launch_gemm derives dh_ld from rp/masked_r; both give rp here.
   }
+  if (!phase_on(kPhaseColProj)) return 0;
   // dB[N, r] = s * dY^T H      (H already carries 1/(1-p))
   if (launch_colproj(dY, H, nullptr, partial, dB, M, N, r, rp, dtype, r, 1, scaling, accumulate, stream)) return 1;
   // dA[r, K] = dH^T drop(X)
@@ -427,6 +437,8 @@ int lora_linear_base(const void* X, const void* W, const void* bias, void* Y, in
   g.inv_keep = 1.f;
   return launch_gemm(g, M, N, K, dtype, sms, stream);
 }
+
+void lora_debug_set_phase_mask(int32_t mask) { g_phase_mask.store(mask & kPhaseAll, std::memory_order_relaxed); }
 
 int lora_dropout_keep_mask(uint8_t* keep_mask, int64_t M, int64_t K, float p, uint64_t seed, uint64_t offset,
                            cudaStream_t stream) {

@@ -393,17 +393,25 @@ __global__ void __launch_bounds__(CP_THREADS)
         phase ^= 1;
       }
     }
-    // acc fragment: (row c = cbk*16 + lane/4 [+8], col j = n*8 + (lane%4)*2 [+1])
+    // acc fragment: (row c = cbk*16 + lane/4 [+8], col j = n*8 + (lane%4)*2 [+1]).
+    // The eight warps add their partial sums in warp order (named barrier 1 between turns):
+    // a fixed summation order keeps dA/dB bit-reproducible, which gradient-checkpoint
+    // recompute and the DDP equality tests rely on.
+    for (int turn = 0; turn < CP_CONSUMERS; ++turn) {
+      if (warp == turn) {
 #pragma unroll
-    for (int cbk = 0; cbk < 4; ++cbk)
+        for (int cbk = 0; cbk < 4; ++cbk)
 #pragma unroll
-      for (int n = 0; n < NB; ++n)
+          for (int n = 0; n < NB; ++n)
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int c = cbk * 16 + (lane >> 2) + ((e >> 1) ? 8 : 0);
-          const int j = n * 8 + (lane & 3) * 2 + (e & 1);
-          atomicAdd(&sout[c * kRPad + j], acc[cbk][n][e]);
-        }
+            for (int e = 0; e < 4; ++e) {
+              const int c = cbk * 16 + (lane >> 2) + ((e >> 1) ? 8 : 0);
+              const int j = n * 8 + (lane & 3) * 2 + (e & 1);
+              sout[c * kRPad + j] += acc[cbk][n][e];
+            }
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(CP_CONSUMERS * 32) : "memory");
+    }
   }
   __syncthreads();
   float* dst = p.partial + (static_cast<size_t>(blockIdx.y) * p.C + c0) * kRPad;
