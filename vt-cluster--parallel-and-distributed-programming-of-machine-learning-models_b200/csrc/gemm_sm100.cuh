@@ -3,13 +3,13 @@
 // K-block and the bias / masked low-rank term applied in the epilogue.
 //
 //   D[M,N] = A1[M,K1] * B1^T  (+ A2[M,rp] * B2[N,rp]^T)  (+ bias[N])
-//            (+ keep[M,N] * inv_keep * (dh[M,:r] * a16[:r,N]))
+//            (+ keep[M,N] * inv_keep * (dh[M,:rp] * a16[N,:rp]^T))
 //
 // forward  (peft lora.Linear.forward):
 //     A1 = X, B1 = W, A2 = H = drop(X) A^T, B2 = s*B, bias = b
 // backward (autograd of the same):
 //     A1 = dY, B1 = W (other major-ness), p == 0: A2 = dH, B2 = A^T
-//                                         p  > 0: masked epilogue with dh, a16, keep bits
+//                                         p  > 0: masked epilogue with dh, A^T, keep bits
 //
 // Roles per CTA (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer
 // (one thread), warp 2 = TMEM allocator, warps 4..7 = epilogue (TMEM -> regs
@@ -45,10 +45,10 @@ struct Params {
   int dtype;       // kDtypeBf16 / kDtypeFp16
   const void* bias;
   // masked low-rank epilogue (backward with dropout)
-  int masked_r;  // 0 = off, else the true rank r (<= 64)
-  const void* dh;  // [M, dh_ld] dtype
+  int masked_r;  // 0 = off, else the true rank r (<= 64); selects the kMasked instantiation
+  const void* dh;  // [M, dh_ld] dtype, dh_ld = padded rank (16/32/64), padding columns zero
   int dh_ld;
-  const void* a16;      // [>= masked_r, N] dtype, row stride N
+  const void* a16;      // A^T as [N, dh_ld] dtype (rank index contiguous), padding columns zero
   const uint8_t* keep;  // [M, N/8] keep bits
   float inv_keep;
 };
@@ -63,6 +63,23 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int&
   n_blk = in_g / gm;
 }
 
+// Warp-level m16n8k16 MMA used by the masked epilogue for the rank-r term.
+__device__ __forceinline__ void mma_16816_bf16(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+__device__ __forceinline__ void mma_16816_f16(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+// kMasked: backward with dropout -- the rank-r term keep/(1-p) .* (dH A) is formed in the
+// epilogue (warp-level MMA + keep-bits) instead of riding the main loop as a K-block.
+template <bool kMasked>
 __global__ void __launch_bounds__(THREADS, 1)
     gemm_lora_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                      const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
@@ -203,10 +220,14 @@ __global__ void __launch_bounds__(THREADS, 1)
     // ===================== epilogue =====================
     const int ew = warp - 4;  // == warp % 4: the TMEM lane quadrant this warp may touch
     uint8_t* my_stage = epi_base + ew * 2 * EPI_BUF_BYTES;
+    // Masked mode stages through buffer 0 only; buffer 1 is the 32x32 fp32 scratch through
+    // which the warp-level MMA result is transposed to one-row-per-thread.
+    float* scratch = reinterpret_cast<float*>(my_stage + EPI_BUF_BYTES);
     uint32_t sbuf = 0;
     uint32_t it = 0;
     const int dtype = p.dtype;
     const int keep_ld = p.N >> 3;
+    const int mk_steps = kMasked ? p.dh_ld / 16 : 0;  // k16 steps of the rank-r product (1, 2 or 4)
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       int m_blk, n_blk;
       tile_coords(tile, num_m, num_n, m_blk, n_blk);
@@ -215,18 +236,25 @@ __global__ void __launch_bounds__(THREADS, 1)
       const int row = m_blk * BM + ew * 32 + lane;
       const bool row_ok = row < p.M;
 
-      // Per-row operand of the masked low-rank term, fetched while the main
-      // loop of this tile is still running.
-      float dhv[16];
-      if (p.masked_r > 0 && p.masked_r <= 16) {
+      // dH rows of this warp as mma.sync A-fragments (2 m16 blocks x up to 4 k16 steps),
+      // fetched while the main loop of this tile is still running.
+      uint32_t dh_frag[2][4][4];
+      if constexpr (kMasked) {
+        const uint32_t* dh32 = reinterpret_cast<const uint32_t*>(p.dh);
 #pragma unroll
-        for (int j = 0; j < 16; ++j) dhv[j] = 0.f;
-        if (row_ok) {
-          const uint16_t* dhp = reinterpret_cast<const uint16_t*>(p.dh) + static_cast<size_t>(row) * p.dh_ld;
+        for (int mb = 0; mb < 2; ++mb)
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (j < p.masked_r) dhv[j] = to_float16bits(dhp[j], dtype) * p.inv_keep;
-        }
+          for (int ks = 0; ks < 4; ++ks) {
+            const int r0 = m_blk * BM + ew * 32 + mb * 16 + (lane >> 2);
+            const int k0 = ks * 16 + (lane & 3) * 2;
+            const bool ks_ok = ks < mk_steps;
+            const size_t o0 = (static_cast<size_t>(r0) * p.dh_ld + k0) >> 1;
+            const size_t o1 = (static_cast<size_t>(r0 + 8) * p.dh_ld + k0) >> 1;
+            dh_frag[mb][ks][0] = (ks_ok && r0 < p.M) ? __ldg(dh32 + o0) : 0u;
+            dh_frag[mb][ks][1] = (ks_ok && r0 + 8 < p.M) ? __ldg(dh32 + o1) : 0u;
+            dh_frag[mb][ks][2] = (ks_ok && r0 < p.M) ? __ldg(dh32 + o0 + 4) : 0u;
+            dh_frag[mb][ks][3] = (ks_ok && r0 + 8 < p.M) ? __ldg(dh32 + o1 + 4) : 0u;
+          }
       }
 
       mbar_wait(&tmem_full[buf], acc_phase, 4);
@@ -236,15 +264,65 @@ __global__ void __launch_bounds__(THREADS, 1)
       for (int cb = 0; cb < BN / 64 && warp_rows_ok; ++cb) {
         const int col0 = n_blk * BN + cb * 64;
         if (col0 >= p.N) break;  // warp-uniform
-        if (lane == 0) bulk_wait_group_read<1>();  // the buffer we are about to overwrite has been read
+        // the staging buffer we are about to overwrite must have been read by its TMA store
+        if (lane == 0) {
+          if constexpr (kMasked) bulk_wait_group_read<0>(); else bulk_wait_group_read<1>();
+        }
         __syncwarp();
-        uint8_t* sdst = my_stage + sbuf * EPI_BUF_BYTES + lane * 128;
+        uint8_t* sdst = my_stage + (kMasked ? 0u : sbuf) * EPI_BUF_BYTES + lane * 128;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           uint32_t v[32];
           tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + buf * BN + cb * 64 + h * 32, v);
-          tmem_ld_wait();
           const int c = col0 + h * 32;
+          if constexpr (kMasked) {
+            // T[32 rows, 32 cols] = dH[32, rp] * A[rp, c..c+31] on the warp's tensor-core path,
+            // overlapping the TMEM load above.  B-fragments come from a16t [N, rp] (j contiguous).
+            float t[2][4][4];
+#pragma unroll
+            for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+              for (int nb = 0; nb < 4; ++nb)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) t[mb][nb][e] = 0.f;
+            const uint32_t* at32 = reinterpret_cast<const uint32_t*>(p.a16);
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+              if (ks < mk_steps) {
+                uint32_t bfr[4][2];
+#pragma unroll
+                for (int nb = 0; nb < 4; ++nb) {
+                  const int col = c + nb * 8 + (lane >> 2);
+                  const size_t o = (static_cast<size_t>(col) * p.dh_ld + ks * 16 + (lane & 3) * 2) >> 1;
+                  bfr[nb][0] = col < p.N ? __ldg(at32 + o) : 0u;
+                  bfr[nb][1] = col < p.N ? __ldg(at32 + o + 4) : 0u;
+                }
+#pragma unroll
+                for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+                  for (int nb = 0; nb < 4; ++nb) {
+                    if (dtype == kDtypeBf16) mma_16816_bf16(t[mb][nb], dh_frag[mb][ks], bfr[nb]);
+                    else mma_16816_f16(t[mb][nb], dh_frag[mb][ks], bfr[nb]);
+                  }
+              }
+            }
+            // fragment (row = mb*16 + lane/4 [+8], col = nb*8 + (lane%4)*2 [+1]) -> scratch,
+            // float4 slots XOR-swizzled by row so that both sides are bank-conflict free.
+            __syncwarp();  // previous chunk's readers are done with the scratch
+#pragma unroll
+            for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+              for (int nb = 0; nb < 4; ++nb)
+#pragma unroll
+                for (int hh = 0; hh < 2; ++hh) {
+                  const int rr = mb * 16 + (lane >> 2) + hh * 8;
+                  const int cc = nb * 8 + (lane & 3) * 2;
+                  float2 val = make_float2(t[mb][nb][hh * 2], t[mb][nb][hh * 2 + 1]);
+                  *reinterpret_cast<float2*>(scratch + rr * 32 + (((cc >> 2) ^ (rr & 7)) << 2) + (cc & 3)) = val;
+                }
+            __syncwarp();
+          }
+          tmem_ld_wait();
           if (p.bias != nullptr) {
             const uint4* bp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.bias) + c);
 #pragma unroll
@@ -261,54 +339,7 @@ __global__ void __launch_bounds__(THREADS, 1)
               }
             }
           }
-          if (p.masked_r > 0) {
-            // low[i] = sum_j dh[row,j] * a16[j, c+i]; added where the dropout mask kept X[row, c+i].
-            float low[32];
-#pragma unroll
-            for (int i = 0; i < 32; ++i) low[i] = 0.f;
-            if (p.masked_r <= 16) {
-#pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                if (j < p.masked_r) {
-                  const uint4* ap = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.a16) +
-                                                                   static_cast<size_t>(j) * p.N + c);
-#pragma unroll
-                  for (int q = 0; q < 4; ++q) {
-                    if (c + q * 8 < p.N) {
-                      const uint4 aw = __ldg(ap + q);
-                      const uint32_t w4[4] = {aw.x, aw.y, aw.z, aw.w};
-#pragma unroll
-                      for (int e = 0; e < 4; ++e) {
-                        const float2 f = unpack2(w4[e], dtype);
-                        low[q * 8 + e * 2] = fmaf(dhv[j], f.x, low[q * 8 + e * 2]);
-                        low[q * 8 + e * 2 + 1] = fmaf(dhv[j], f.y, low[q * 8 + e * 2 + 1]);
-                      }
-                    }
-                  }
-                }
-              }
-            } else {
-              // Wide ranks: dh row is re-read from L1/L2 instead of living in registers.
-              const uint16_t* dhp = reinterpret_cast<const uint16_t*>(p.dh) + static_cast<size_t>(row) * p.dh_ld;
-              for (int j = 0; j < p.masked_r; ++j) {
-                const float d = row_ok ? to_float16bits(dhp[j], dtype) * p.inv_keep : 0.f;
-                const uint4* ap = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.a16) +
-                                                                 static_cast<size_t>(j) * p.N + c);
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  if (c + q * 8 < p.N) {
-                    const uint4 aw = __ldg(ap + q);
-                    const uint32_t w4[4] = {aw.x, aw.y, aw.z, aw.w};
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                      const float2 f = unpack2(w4[e], dtype);
-                      low[q * 8 + e * 2] = fmaf(d, f.x, low[q * 8 + e * 2]);
-                      low[q * 8 + e * 2 + 1] = fmaf(d, f.y, low[q * 8 + e * 2 + 1]);
-                    }
-                  }
-                }
-              }
-            }
+          if constexpr (kMasked) {
             uint32_t kbits = 0;
             if (row_ok) {
               const uint8_t* kp = p.keep + static_cast<size_t>(row) * keep_ld + (c >> 3);
@@ -317,8 +348,14 @@ __global__ void __launch_bounds__(THREADS, 1)
                 if (c + q * 8 < p.N) kbits |= static_cast<uint32_t>(__ldg(kp + q)) << (8 * q);
             }
 #pragma unroll
-            for (int i = 0; i < 32; ++i)
-              if ((kbits >> i) & 1u) v[i] = __float_as_uint(__uint_as_float(v[i]) + low[i]);
+            for (int f = 0; f < 8; ++f) {
+              const float4 t4 = *reinterpret_cast<const float4*>(scratch + lane * 32 + ((f ^ (lane & 7)) << 2));
+              const float tv[4] = {t4.x, t4.y, t4.z, t4.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                if ((kbits >> (f * 4 + e)) & 1u)
+                  v[f * 4 + e] = __float_as_uint(fmaf(tv[e], p.inv_keep, __uint_as_float(v[f * 4 + e])));
+            }
           }
           // fp32 -> 16-bit, 128B-swizzled staging (chunk index XOR row-in-atom)
 #pragma unroll
@@ -335,7 +372,7 @@ __global__ void __launch_bounds__(THREADS, 1)
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
-          tma_store_2d(&tmD, my_stage + sbuf * EPI_BUF_BYTES, col0, m_blk * BM + ew * 32);
+          tma_store_2d(&tmD, my_stage + (kMasked ? 0u : sbuf) * EPI_BUF_BYTES, col0, m_blk * BM + ew * 32);
           bulk_commit_group();
         }
         sbuf ^= 1u;

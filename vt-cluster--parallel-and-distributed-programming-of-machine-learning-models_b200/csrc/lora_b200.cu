@@ -101,7 +101,8 @@ int device_setup(int* sm_count) {
     CUDA_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
     if (major != 10) return fail("this library contains sm_100a code only; device %d is compute capability %d.x", dev, major);
     CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel, gemm::SMEM_BYTES));
+    CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false>, gemm::SMEM_BYTES));
+    CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<true>, gemm::SMEM_BYTES));
 #define OPT_IN_SKINNY(BF, RP)                                                                     \
   CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP>, skinny::rp_smem_bytes<RP>()));             \
   CUDA_TRY(opt_in_smem(skinny::colproj_kernel<BF, RP>, skinny::cp_smem_bytes<RP>()));
@@ -309,7 +310,10 @@ int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, 
 
   const long long tiles = ((M + gemm::BM - 1) / gemm::BM) * ((N + gemm::BN - 1) / gemm::BN);
   const int grid = static_cast<int>(std::min<long long>(tiles, sm_count));
-  gemm::gemm_lora_kernel<<<grid, gemm::THREADS, gemm::SMEM_BYTES, stream>>>(tmA1, tmB1, tmA2, tmB2, tmD, p);
+  if (p.masked_r > 0)
+    gemm::gemm_lora_kernel<true><<<grid, gemm::THREADS, gemm::SMEM_BYTES, stream>>>(tmA1, tmB1, tmA2, tmB2, tmD, p);
+  else
+    gemm::gemm_lora_kernel<false><<<grid, gemm::THREADS, gemm::SMEM_BYTES, stream>>>(tmA1, tmB1, tmA2, tmB2, tmD, p);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -403,7 +407,7 @@ int lora_linear_bwd(const void* dY, const void* X, const void* W, const float* A
       g.rp = 0;
       g.masked_r = r;
       g.dh = dH;
-      g.a16 = ws + w.a16;
+      g.a16 = ws + w.a16t;  // [K, rp]: rank index contiguous, as the epilogue's B-fragments want
       g.keep = keep;
     } else {
       g.A2 = dH;

@@ -103,15 +103,17 @@ __global__ void pack_adapters_kernel(const float* __restrict__ A, const float* _
 
 // ---------------------------------------------------------------------------
 // rowproj: Out[M, kRPad] = out_scale * (keep .* Act)[M, C] * P[kRPad, C]^T
-// One CTA per 64 rows; warp 4 is the TMA producer, warps 0..3 own 16 rows each.
-// With dropout on, each warp first zeroes the dropped elements of its own rows
-// in shared memory (one Philox call per 8 elements) and publishes the keep-bits.
+// One CTA per 64 rows.  Warp 8 is the TMA producer; consumer warps w and w+4 form a pair
+// that owns rows 16(w%4)..+15: each masks half of the slab's 16-byte chunks (one Philox call
+// per 8 elements, drawn BEFORE waiting for the tile so the ALU work hides under the TMA
+// latency), the pair meets on a named barrier, then each takes half of the tile's k16 steps.
+// The two partial accumulators are summed through shared memory at the end.
 // ---------------------------------------------------------------------------
 constexpr int RP_BM = 64;
 constexpr int RP_BK = 64;
 constexpr int RP_STAGES = 6;
 constexpr int RP_ACT_BYTES = RP_BM * 128;  // 8 KiB
-constexpr int RP_CONSUMERS = 4;
+constexpr int RP_CONSUMERS = 8;
 constexpr int RP_THREADS = (RP_CONSUMERS + 1) * 32;
 template <int kRPad>
 __host__ __device__ constexpr int rp_slot_bytes() {
@@ -119,7 +121,7 @@ __host__ __device__ constexpr int rp_slot_bytes() {
 }
 template <int kRPad>
 __host__ __device__ constexpr int rp_smem_bytes() {
-  return RP_STAGES * rp_slot_bytes<kRPad>() + 1024 + 256;
+  return RP_STAGES * rp_slot_bytes<kRPad>() + RP_BM * kRPad * 4 + 1024 + 256;
 }
 
 struct RowProjParams {
@@ -140,7 +142,8 @@ __global__ void __launch_bounds__(RP_THREADS)
   constexpr int NB = kRPad / 8;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + RP_STAGES * SLOT);
+  float* sred = reinterpret_cast<float*>(smem + RP_STAGES * SLOT);  // [64 rows][kRPad] pair reduction
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + RP_STAGES * SLOT + RP_BM * kRPad * 4);
   uint64_t* empty = full + RP_STAGES;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -175,6 +178,8 @@ __global__ void __launch_bounds__(RP_THREADS)
     return;
   }
 
+  const int slab = warp & 3;   // 16-row slab of the tile
+  const int half = warp >> 2;  // which half of the slab's chunks / k-steps this warp takes
   float acc[NB][4];
 #pragma unroll
   for (int n = 0; n < NB; ++n)
@@ -184,31 +189,42 @@ __global__ void __launch_bounds__(RP_THREADS)
   const int keep_ld = p.C >> 3;
   uint32_t stage = 0, phase = 0;
   for (int kb = 0; kb < nk; ++kb) {
+    // keep-bits of this warp's 2 chunks per lane: independent of the data, so drawn first
+    uint32_t bits[2] = {0xFFu, 0xFFu};
+    if (p.dropout) {
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int idx = half * 64 + lane + 32 * i;
+        const int m = m0 + slab * 16 + (idx >> 3), c = kb * RP_BK + (idx & 7) * 8;
+        if (m < p.M && c < p.C) {
+          const uint64_t g = (static_cast<uint64_t>(m) * static_cast<uint64_t>(p.C) + static_cast<uint64_t>(c)) >> 3;
+          bits[i] = dropout_keep_bits(g, p.seed, p.offset, p.thresh16);
+          p.keep_out[static_cast<size_t>(m) * keep_ld + (c >> 3)] = static_cast<uint8_t>(bits[i]);
+        }
+      }
+    }
     mbar_wait(&full[stage], phase, 12);
     uint8_t* act = smem + stage * SLOT;
     uint8_t* pt = act + RP_ACT_BYTES;
     if (p.dropout) {
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int idx = lane + 32 * i;
-        const int R = warp * 16 + (idx >> 3), ch = idx & 7;
-        const int m = m0 + R, c = kb * RP_BK + ch * 8;
-        if (m < p.M && c < p.C) {
-          const uint64_t g = (static_cast<uint64_t>(m) * static_cast<uint64_t>(p.C) + static_cast<uint64_t>(c)) >> 3;
-          const uint32_t bits = dropout_keep_bits(g, p.seed, p.offset, p.thresh16);
+      for (int i = 0; i < 2; ++i) {
+        const int idx = half * 64 + lane + 32 * i;
+        const int R = slab * 16 + (idx >> 3), ch = idx & 7;
+        if (bits[i] != 0xFFu) {
           uint4* ptr = reinterpret_cast<uint4*>(act + R * 128 + ((ch ^ (R & 7)) << 4));
-          *ptr = apply_keep(*ptr, bits);
-          p.keep_out[static_cast<size_t>(m) * keep_ld + (c >> 3)] = static_cast<uint8_t>(bits);
+          *ptr = apply_keep(*ptr, bits[i]);
         }
       }
-      __syncwarp();
+      asm volatile("bar.sync %0, 64;" ::"r"(1 + slab) : "memory");  // the pair's slab is fully masked
     }
     const uint32_t act_u = smem_u32(act), pt_u = smem_u32(pt);
 #pragma unroll
-    for (int ks = 0; ks < RP_BK / 16; ++ks) {
+    for (int kk = 0; kk < 2; ++kk) {
+      const int ks = half * 2 + kk;
       uint32_t a[4];
       {
-        const int R = warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+        const int R = slab * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
         const int ch = ks * 2 + (lane >> 4);
         ldsm_x4(act_u + R * 128 + ((ch ^ (R & 7)) << 4), a);
       }
@@ -230,18 +246,33 @@ __global__ void __launch_bounds__(RP_THREADS)
     }
   }
 
-  // acc fragment: (row = lane/4 [+8], col = n*8 + (lane%4)*2 [+1])
-  uint32_t* out = reinterpret_cast<uint32_t*>(p.out);
-  const int r0 = m0 + warp * 16 + (lane >> 2);
+  // acc fragment: (row = lane/4 [+8], col = n*8 + (lane%4)*2 [+1]); half 1 hands its partial
+  // sums to half 0 through smem (fixed order -> bit-reproducible).
+  const int rloc = slab * 16 + (lane >> 2);
+  if (half == 1) {
 #pragma unroll
-  for (int n = 0; n < NB; ++n) {
-    const int col = n * 8 + (lane & 3) * 2;
-    if (r0 < p.M)
-      out[(static_cast<size_t>(r0) * kRPad + col) >> 1] =
-          pack2(acc[n][0] * p.out_scale, acc[n][1] * p.out_scale, kBf16 ? kDtypeBf16 : kDtypeFp16);
-    if (r0 + 8 < p.M)
-      out[(static_cast<size_t>(r0 + 8) * kRPad + col) >> 1] =
-          pack2(acc[n][2] * p.out_scale, acc[n][3] * p.out_scale, kBf16 ? kDtypeBf16 : kDtypeFp16);
+    for (int n = 0; n < NB; ++n) {
+      const int col = n * 8 + (lane & 3) * 2;
+      *reinterpret_cast<float2*>(sred + rloc * kRPad + col) = make_float2(acc[n][0], acc[n][1]);
+      *reinterpret_cast<float2*>(sred + (rloc + 8) * kRPad + col) = make_float2(acc[n][2], acc[n][3]);
+    }
+  }
+  asm volatile("bar.sync %0, 64;" ::"r"(1 + slab) : "memory");
+  if (half == 0) {
+    uint32_t* out = reinterpret_cast<uint32_t*>(p.out);
+    const int r0 = m0 + rloc;
+#pragma unroll
+    for (int n = 0; n < NB; ++n) {
+      const int col = n * 8 + (lane & 3) * 2;
+      const float2 o0 = *reinterpret_cast<const float2*>(sred + rloc * kRPad + col);
+      const float2 o1 = *reinterpret_cast<const float2*>(sred + (rloc + 8) * kRPad + col);
+      if (r0 < p.M)
+        out[(static_cast<size_t>(r0) * kRPad + col) >> 1] =
+            pack2((acc[n][0] + o0.x) * p.out_scale, (acc[n][1] + o0.y) * p.out_scale, kBf16 ? kDtypeBf16 : kDtypeFp16);
+      if (r0 + 8 < p.M)
+        out[(static_cast<size_t>(r0 + 8) * kRPad + col) >> 1] =
+            pack2((acc[n][2] + o1.x) * p.out_scale, (acc[n][3] + o1.y) * p.out_scale, kBf16 ? kDtypeBf16 : kDtypeFp16);
+    }
   }
 }
 
@@ -329,23 +360,36 @@ __global__ void __launch_bounds__(CP_THREADS)
         for (int e = 0; e < 4; ++e) acc[cbk][n][e] = 0.f;
 
     const int keep_ld = p.C >> 3;
+    // keep-bytes of this warp's 16 rows x 8 chunks (4 per lane), fetched one tile ahead so the
+    // global-load latency never sits between a tile's arrival and its MMAs.
+    auto load_keep = [&](int mt, uint32_t (&kb)[4]) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int idx = lane + 32 * i;
+        const int m = mt + warp * 16 + (idx >> 3), c = c0 + (idx & 7) * 8;
+        kb[i] = (m < p.M && c < p.C) ? __ldg(p.keep + static_cast<size_t>(m) * keep_ld + (c >> 3)) : 0xFFu;
+      }
+    };
+    uint32_t kcur[4] = {0xFFu, 0xFFu, 0xFFu, 0xFFu}, knext[4] = {0xFFu, 0xFFu, 0xFFu, 0xFFu};
+    if (p.keep != nullptr && nt > 0) load_keep(m_begin, kcur);
     uint32_t stage = 0, phase = 0;
     for (int t = 0; t < nt; ++t) {
+      const int mt = m_begin + t * CP_BM;
+      if (p.keep != nullptr && t + 1 < nt) load_keep(mt + CP_BM, knext);
       mbar_wait(&full[stage], phase, 22);
       uint8_t* act = smem + stage * SLOT;
-      const int mt = m_begin + t * CP_BM;
       if (p.keep != nullptr) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const int idx = lane + 32 * i;
           const int R = warp * 16 + (idx >> 3), ch = idx & 7;
-          const int m = mt + R, c = c0 + ch * 8;
-          if (m < p.M && c < p.C) {
-            const uint32_t bits = __ldg(p.keep + static_cast<size_t>(m) * keep_ld + (c >> 3));
+          if (kcur[i] != 0xFFu) {
             uint4* ptr = reinterpret_cast<uint4*>(act + R * 128 + ((ch ^ (R & 7)) << 4));
-            *ptr = apply_keep(*ptr, bits);
+            *ptr = apply_keep(*ptr, kcur[i]);
           }
         }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) kcur[i] = knext[i];
         __syncwarp();
       }
       // Rows of the last tile of a split that belong to the next split (or lie

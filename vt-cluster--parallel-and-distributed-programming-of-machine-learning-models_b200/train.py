@@ -1,0 +1,158 @@
+"""Step loop and data-parallel wrapper around a LoRA-adapted causal LM.
+
+Restates, for a single 8xB200 box, what the reference gets from HF Trainer + accelerate with
+its TrainingArguments (finetune_lora_distilgpt2.py:130-158): AdamW(lr, betas (0.9, 0.999),
+eps 1e-8, weight_decay 0), linear LR decay to zero, gradient-norm clip 1.0, gradient
+accumulation with the all-reduce skipped on non-boundary micro-steps, loss = mean
+cross-entropy over shifted tokens whose label is not -100 (DataCollatorForLanguageModeling
+with mlm=False, finetune_lora_distilgpt2.py:114).  Under DDP only the adapter parameters
+(requires_grad) enter the reducer; the bucketed all-reduce runs on NCCL over NVLink and
+overlaps the remaining backward (torch DDP's autograd hooks fire as each fused LoRA node
+returns its dA/dB).
+
+This module is host-side plumbing: it runs on whatever device the model lives on, so the CPU
+test-suite can drive it with gloo (world_size 2) and the oracle's layer.
+"""
+from __future__ import annotations
+
+import contextlib
+import os
+from dataclasses import dataclass
+from typing import Callable, Dict, Iterable, List, Optional
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+@dataclass
+class TrainConfig:
+    lr: float = 5e-5  # finetune_lora_distilgpt2.py:16
+    accum: int = 32  # finetune_lora_distilgpt2.py:15 (--accum)
+    max_grad_norm: float = 1.0  # HF Trainer default; DeepSpeed gradient_clipping 1.0 (finetune_lora_opt_pp.py:197)
+    total_steps: Optional[int] = None  # for the linear decay; None -> number of steps run
+    betas: tuple = (0.9, 0.999)
+    eps: float = 1e-8
+    weight_decay: float = 0.0
+    constant_lr: bool = False  # the OPT pipeline script keeps lr constant (finetune_lora_opt_pp.py:207)
+
+
+def causal_lm_loss(logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+    shift_logits = logits[:, :-1, :].contiguous().float()
+    shift_labels = labels[:, 1:].contiguous()
+    return F.cross_entropy(shift_logits.view(-1, shift_logits.size(-1)), shift_labels.view(-1), ignore_index=-100)
+
+
+def synthetic_batches(n: int, batch: int, seq: int, vocab: int, pad_id: int, seed: int, device="cpu") -> List[Dict]:
+    """Random token batches of the named shape (no network for datasets): ids exclude the pad id,
+    attention mask all ones, labels = ids (nothing padded, so nothing is -100)."""
+    g = torch.Generator().manual_seed(seed)
+    out = []
+    for _ in range(n):
+        ids = torch.randint(0, vocab - 1, (batch, seq), generator=g)
+        ids = ids + (ids >= pad_id).long()  # skip pad_id
+        out.append({"input_ids": ids.to(device), "attention_mask": torch.ones_like(ids).to(device),
+                    "labels": ids.clone().to(device)})
+    return out
+
+
+def trainable_parameters(model: nn.Module):
+    return [p for p in model.parameters() if p.requires_grad]
+
+
+def wrap_ddp(model: nn.Module, device: Optional[torch.device] = None, bucket_cap_mb: int = 25,
+             static_graph: bool = False) -> nn.Module:
+    """torch DDP the way HF Trainer configures it for the reference
+    (ddp_find_unused_parameters=False, finetune_lora_distilgpt2.py:142): frozen base weights
+    never enter the reducer, so the only traffic is the adapter-gradient bucket
+    (1.6 MB for distilgpt2 r=8)."""
+    from torch.nn.parallel import DistributedDataParallel as DDP
+
+    kw = dict(find_unused_parameters=False, bucket_cap_mb=bucket_cap_mb, gradient_as_bucket_view=True,
+              static_graph=static_graph)
+    if device is not None and device.type == "cuda":
+        return DDP(model, device_ids=[device.index], output_device=device.index, **kw)
+    return DDP(model, **kw)
+
+
+class Trainer:
+    """Minimal stand-in for transformers.Trainer on this path (model(**batch) -> loss, backward,
+    accumulate, reduce, clip, AdamW, linear decay)."""
+
+    def __init__(self, model: nn.Module, cfg: TrainConfig, on_step_end: Optional[Callable] = None):
+        self.model = model
+        self.cfg = cfg
+        self.params = trainable_parameters(model)
+        self.opt = torch.optim.AdamW(self.params, lr=cfg.lr, betas=cfg.betas, eps=cfg.eps,
+                                     weight_decay=cfg.weight_decay)
+        self.sched = None
+        self.global_step = 0
+        self.on_step_end = on_step_end
+
+    def _ensure_sched(self, n_steps: int):
+        if self.sched is None:
+            total = self.cfg.total_steps or n_steps
+            if self.cfg.constant_lr:
+                fn = lambda s: 1.0
+            else:
+                fn = lambda s: max(0.0, (total - s) / max(1, total))
+            self.sched = torch.optim.lr_scheduler.LambdaLR(self.opt, fn)
+
+    def micro_step(self, batch: Dict, sync: bool) -> torch.Tensor:
+        ctx = contextlib.nullcontext()
+        if not sync and hasattr(self.model, "no_sync"):
+            ctx = self.model.no_sync()  # accumulation micro-step: no all-reduce
+        with ctx:
+            out = self.model(input_ids=batch["input_ids"], attention_mask=batch.get("attention_mask"))
+            logits = out.logits if hasattr(out, "logits") else out
+            loss = causal_lm_loss(logits, batch["labels"]) / self.cfg.accum
+            loss.backward()
+        return loss.detach()
+
+    def optimizer_step(self):
+        torch.nn.utils.clip_grad_norm_(self.params, self.cfg.max_grad_norm)
+        self.opt.step()
+        self.sched.step()
+        self.opt.zero_grad(set_to_none=True)
+        self.global_step += 1
+
+    def train(self, batches: Iterable[Dict]) -> List[torch.Tensor]:
+        batches = list(batches)
+        accum = self.cfg.accum
+        n_steps = len(batches) // accum
+        self._ensure_sched(n_steps)
+        self.model.train()
+        losses = []
+        for step in range(n_steps):
+            total = None
+            for micro in range(accum):
+                l = self.micro_step(batches[step * accum + micro], sync=(micro == accum - 1))
+                total = l if total is None else total + l
+            self.optimizer_step()
+            losses.append(total)  # stays on the device: no host sync inside the loop
+            if self.on_step_end is not None:
+                self.on_step_end(self, step, total)
+        return losses
+
+
+def init_distributed(backend: Optional[str] = None):
+    """env:// rendezvous as in finetune_lora_distilgpt2.py:35-45, NCCL on GPUs (gloo only in the
+    CPU tests).  Returns (rank, world, local_rank)."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        kw = {}
+        if backend == "nccl":
+            torch.cuda.set_device(local)
+            kw["device_id"] = torch.device("cuda", local)
+        dist.init_process_group(backend=backend, init_method="env://", rank=rank, world_size=world, **kw)
+        x = torch.ones(1, device=kw.get("device_id", "cpu"))
+        dist.all_reduce(x)  # collective sanity check, finetune_lora_distilgpt2.py:50-54
+        assert int(x.item()) == world
+    return rank, world, local
