@@ -187,8 +187,9 @@ def run_point(a, pkg, rank, world, device, emit=True):
         import torch.distributed as dist
 
     def step(i):
-        Y, H, keep = bind.linear_fwd(x, W, b, A, B, s, p, 1, 4 * i, a.conv1d, ws)
-        bind.linear_bwd(dy, x, W, A, B, H, keep, s, p, a.conv1d, ws, need_dx=True, dA=dA, dB=dB)
+        Y, H, keep, xd = bind.linear_fwd(x, W, b, A, B, s, p, 1, 4 * i, a.conv1d, ws, save_xd=True)
+        bind.linear_bwd(dy, xd if xd is not None else x, W, A, B, H, keep, s, p, a.conv1d, ws, need_dx=True, dA=dA,
+                        dB=dB, x_is_dropped=xd is not None)
         if dist_on:  # the path's one exchange step under DDP: average the adapter gradients
             bucket[: r * K].copy_(dA.view(-1))
             bucket[r * K:].copy_(dB.view(-1))
@@ -226,7 +227,8 @@ def run_point(a, pkg, rank, world, device, emit=True):
         n_rep = max(20, a.steps)
         for _ in range(5):
             bind.lib().lora_linear_fwd(x.data_ptr(), W.data_ptr(), b.data_ptr(), A.data_ptr(), B.data_ptr(),
-                                       Ybuf.data_ptr(), H.data_ptr(), keep.data_ptr(), M, K, N, r, s, p, 1, 0,
+                                       Ybuf.data_ptr(), H.data_ptr(), keep.data_ptr() if keep is not None else None,
+                                       None, M, K, N, r, s, p, 1, 0,
                                        bind.dtype_code(dtype), int(a.conv1d), ws.data_ptr(), ws.numel(),
                                        torch.cuda.current_stream().cuda_stream)
         torch.cuda.synchronize()
@@ -234,7 +236,8 @@ def run_point(a, pkg, rank, world, device, emit=True):
         g0.record()
         for _ in range(n_rep):
             bind.lib().lora_linear_fwd(x.data_ptr(), W.data_ptr(), b.data_ptr(), A.data_ptr(), B.data_ptr(),
-                                       Ybuf.data_ptr(), H.data_ptr(), keep.data_ptr(), M, K, N, r, s, p, 1, 0,
+                                       Ybuf.data_ptr(), H.data_ptr(), keep.data_ptr() if keep is not None else None,
+                                       None, M, K, N, r, s, p, 1, 0,
                                        bind.dtype_code(dtype), int(a.conv1d), ws.data_ptr(), ws.numel(),
                                        torch.cuda.current_stream().cuda_stream)
         g1.record()

@@ -56,10 +56,13 @@ size_t lora_linear_workspace_bytes(int64_t M, int64_t K, int64_t N, int32_t r);
  *     Y = X W^T + bias + scaling * H B^T
  * p > 0 draws the dropout mask from Philox4x32-10 keyed by (seed, offset) and
  * writes the keep-bits to keep_mask (needed by backward); p == 0 ignores
- * keep_mask (may be NULL).
+ * keep_mask (may be NULL).  Xd (optional, [M,K], may be NULL) receives
+ * keep .* X -- the tensor torch autograd would save for lora_A's weight
+ * gradient -- so that backward need not re-apply the mask; only written
+ * when p > 0.
  */
 int lora_linear_fwd(const void* X, const void* W, const void* bias, const float* A, const float* B, void* Y, void* H,
-                    uint8_t* keep_mask, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p,
+                    uint8_t* keep_mask, void* Xd, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p,
                     uint64_t seed, uint64_t offset, int32_t dtype, int32_t w_is_KN, void* workspace,
                     size_t workspace_bytes, cudaStream_t stream);
 
@@ -70,12 +73,13 @@ int lora_linear_fwd(const void* X, const void* W, const void* bias, const float*
  *     dB = scaling * dY^T H               dA = dH^T dropout_p(X)
  * No dW, no dbias (base layer frozen, LoraConfig bias="none").  dX may be NULL
  * (input needs no gradient).  dA [r,K] and dB [N,r] are fp32 and are
- * overwritten, or added to when accumulate != 0.
+ * overwritten, or added to when accumulate != 0.  X is the forward input, or,
+ * with x_is_dropped != 0, the Xd tensor forward wrote (keep .* X).
  */
 int lora_linear_bwd(const void* dY, const void* X, const void* W, const float* A, const float* B, const void* H,
                     const uint8_t* keep_mask, void* dX, float* dA, float* dB, int64_t M, int64_t K, int64_t N,
                     int32_t r, float scaling, float p, int32_t dtype, int32_t w_is_KN, int32_t accumulate,
-                    void* workspace, size_t workspace_bytes, cudaStream_t stream);
+                    int32_t x_is_dropped, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 
 /*
  * Frozen projection alone, Y = X W^T + bias: the base_layer call of peft's

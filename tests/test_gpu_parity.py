@@ -94,9 +94,19 @@ def _run_fwd_bwd(pkg, M, K, N, r, p, w_is_KN, dtype, bias, b_zero=False, seed=11
     d = to_dev(c, dtype)
     s = 16.0 / r
     ws = torch.empty(pkg.binding.workspace_bytes(M, K, N, r), dtype=torch.uint8, device="cuda")
-    Y, H, keep = pkg.binding.linear_fwd(d["x"], d["W"], d["b"], d["A"], d["B"], s, p, seed, offset, w_is_KN, ws)
+    Y, H, keep, xd = pkg.binding.linear_fwd(d["x"], d["W"], d["b"], d["A"], d["B"], s, p, seed, offset, w_is_KN, ws,
+                                            save_xd=True)
     dX, dA, dB = pkg.binding.linear_bwd(d["dy"], d["x"], d["W"], d["A"], d["B"], H, keep, s, p, w_is_KN, ws)
     torch.cuda.synchronize()
+    if p > 0:
+        # backward from the saved dropout(X) must give bit-identical adapter gradients
+        bits = torch.from_numpy(np.unpackbits(keep.cpu().numpy(), axis=1, bitorder="little")).bool()
+        assert torch.equal(xd.cpu(), torch.where(bits, d["x"].cpu(), torch.zeros((), dtype=d["x"].dtype)))
+        _, dA2, dB2 = pkg.binding.linear_bwd(d["dy"], xd, d["W"], d["A"], d["B"], H, keep, s, p, w_is_KN, ws,
+                                             need_dx=False, x_is_dropped=True)
+        assert torch.equal(dA2, dA) and torch.equal(dB2, dB)
+    else:
+        assert xd is None
     keep_ref = torch.from_numpy(philox.keep_mask(M, K, p, seed, offset)) if p > 0 else None
     if p > 0:
         assert np.array_equal(keep.cpu().numpy(), philox.keep_bytes(M, K, p, seed, offset))

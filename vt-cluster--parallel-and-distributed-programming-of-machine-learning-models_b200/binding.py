@@ -25,13 +25,13 @@ _SIGNATURES = {
     "lora_linear_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64, c_int32]),
     "lora_linear_fwd": (
         c_int,
-        [c_void_p] * 8 + [c_int64, c_int64, c_int64, c_int32, c_float, c_float, c_uint64, c_uint64, c_int32, c_int32,
+        [c_void_p] * 9 + [c_int64, c_int64, c_int64, c_int32, c_float, c_float, c_uint64, c_uint64, c_int32, c_int32,
                           c_void_p, c_size_t, c_void_p],
     ),
     "lora_linear_bwd": (
         c_int,
-        [c_void_p] * 10 + [c_int64, c_int64, c_int64, c_int32, c_float, c_float, c_int32, c_int32, c_int32, c_void_p,
-                           c_size_t, c_void_p],
+        [c_void_p] * 10 + [c_int64, c_int64, c_int64, c_int32, c_float, c_float, c_int32, c_int32, c_int32, c_int32,
+                           c_void_p, c_size_t, c_void_p],
     ),
     "lora_linear_base": (c_int, [c_void_p] * 4 + [c_int64, c_int64, c_int64, c_int32, c_int32, c_void_p]),
     "lora_debug_set_phase_mask": (None, [c_int32]),
@@ -96,8 +96,9 @@ def workspace_bytes(M: int, K: int, N: int, r: int) -> int:
     return int(lib().lora_linear_workspace_bytes(M, K, N, r))
 
 
-def linear_fwd(x2d, W, bias, A, B, scaling, p, seed, offset, w_is_KN, workspace, out=None):
-    """Y, H, keep = fused forward.  x2d [M,K] 16-bit, A [r,K] / B [N,r] fp32."""
+def linear_fwd(x2d, W, bias, A, B, scaling, p, seed, offset, w_is_KN, workspace, out=None, save_xd=False):
+    """Y, H, keep[, Xd] = fused forward.  x2d [M,K] 16-bit, A [r,K] / B [N,r] fp32.
+    save_xd: also return keep .* X (None when p == 0) for linear_bwd(..., x_is_dropped=True)."""
     _need_cuda(x2d, W, bias, A, B, workspace)
     M, K = x2d.shape
     N = W.shape[1] if w_is_KN else W.shape[0]
@@ -105,18 +106,22 @@ def linear_fwd(x2d, W, bias, A, B, scaling, p, seed, offset, w_is_KN, workspace,
     Y = out if out is not None else torch.empty((M, N), dtype=x2d.dtype, device=x2d.device)
     H = torch.empty((M, rpad(r)), dtype=x2d.dtype, device=x2d.device)
     keep = torch.empty((M, K // 8), dtype=torch.uint8, device=x2d.device) if p > 0 else None
+    xd = torch.empty_like(x2d) if (save_xd and p > 0) else None
     rc = lib().lora_linear_fwd(
-        _ptr(x2d), _ptr(W), _ptr(bias), _ptr(A), _ptr(B), _ptr(Y), _ptr(H), _ptr(keep), M, K, N, r, float(scaling),
+        _ptr(x2d), _ptr(W), _ptr(bias), _ptr(A), _ptr(B), _ptr(Y), _ptr(H), _ptr(keep), _ptr(xd), M, K, N, r,
+        float(scaling),
         float(p), int(seed), int(offset), dtype_code(x2d.dtype), int(bool(w_is_KN)), _ptr(workspace),
         workspace.numel() * workspace.element_size(), _stream(),
     )
     _check(rc, "lora_linear_fwd")
+    if save_xd:
+        return Y, H, keep, xd
     return Y, H, keep
 
 
 def linear_bwd(dy2d, x2d, W, A, B, H, keep, scaling, p, w_is_KN, workspace, need_dx=True, dA=None, dB=None,
-               accumulate=False):
-    """dX (or None), dA [r,K] fp32, dB [N,r] fp32."""
+               accumulate=False, x_is_dropped=False):
+    """dX (or None), dA [r,K] fp32, dB [N,r] fp32.  x2d is X, or forward's Xd with x_is_dropped."""
     _need_cuda(dy2d, x2d, W, A, B, H, keep, workspace)
     M, K = x2d.shape
     N = dy2d.shape[1]
@@ -129,7 +134,7 @@ def linear_bwd(dy2d, x2d, W, A, B, H, keep, scaling, p, w_is_KN, workspace, need
     rc = lib().lora_linear_bwd(
         _ptr(dy2d), _ptr(x2d), _ptr(W), _ptr(A), _ptr(B), _ptr(H), _ptr(keep), _ptr(dX), _ptr(dA), _ptr(dB), M, K, N,
         r, float(scaling), float(p), dtype_code(x2d.dtype), int(bool(w_is_KN)), int(bool(accumulate)),
-        _ptr(workspace), workspace.numel() * workspace.element_size(), _stream(),
+        int(bool(x_is_dropped)), _ptr(workspace), workspace.numel() * workspace.element_size(), _stream(),
     )
     _check(rc, "lora_linear_bwd")
     return dX, dA, dB

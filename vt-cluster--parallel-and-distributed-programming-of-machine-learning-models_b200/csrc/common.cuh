@@ -257,6 +257,26 @@ __host__ __device__ __forceinline__ uint32_t dropout_keep_bits(uint64_t g, uint6
   }
   return bits;
 }
+#ifdef __CUDACC__
+// Same draw, delivered as four AND-masks for the four 32-bit words of a 16-byte chunk of
+// 16-bit elements (0xFFFF per surviving element) plus the packed keep-bits; the per-halfword
+// compares run on the SIMD video path instead of eight scalar compare/select chains.
+__device__ __forceinline__ uint32_t dropout_keep_masks(uint64_t g, uint64_t seed, uint64_t offset, uint32_t thresh16,
+                                                       uint32_t (&mask)[4]) {
+  uint32_t r[4];
+  philox4x32_10(static_cast<uint32_t>(g), static_cast<uint32_t>(g >> 32), static_cast<uint32_t>(offset),
+                static_cast<uint32_t>(offset >> 32), static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32),
+                r);
+  const uint32_t t2 = thresh16 | (thresh16 << 16);
+  uint32_t bits = 0;
+#pragma unroll
+  for (int w = 0; w < 4; ++w) {
+    mask[w] = __vcmpgeu2(r[w], t2);  // 0xFFFF where lane >= thresh (unsigned)
+    bits |= ((mask[w] & 1u) | ((mask[w] >> 15) & 2u)) << (2 * w);
+  }
+  return bits;
+}
+#endif
 
 // ---------------------------------------------------------------------------
 // 16-bit float helpers (dtype is a runtime tag in the tcgen05 kernel)

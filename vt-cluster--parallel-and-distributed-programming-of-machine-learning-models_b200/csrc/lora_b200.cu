@@ -184,21 +184,27 @@ int launch_pack(const float* A, const float* B, uint8_t* ws, const Workspace& w,
 }
 
 template <bool BF, int RP>
-int launch_rowproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmP, const skinny::RowProjParams& p,
-                     cudaStream_t stream) {
+int launch_rowproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmP, const CUtensorMap& tmXd,
+                     const skinny::RowProjParams& p, cudaStream_t stream) {
   const int grid = (p.M + skinny::RP_BM - 1) / skinny::RP_BM;
-  skinny::rowproj_kernel<BF, RP><<<grid, skinny::RP_THREADS, skinny::rp_smem_bytes<RP>(), stream>>>(tmAct, tmP, p);
+  skinny::rowproj_kernel<BF, RP><<<grid, skinny::RP_THREADS, skinny::rp_smem_bytes<RP>(), stream>>>(tmAct, tmP, tmXd, p);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
 
 // out[M, rp] = out_scale * (keep .* act)[M, C] * P[rp, C]^T
-int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out, int64_t M, int64_t C, int rp,
-                   int dtype, float out_scale, float p, uint64_t seed, uint64_t offset, cudaStream_t stream) {
-  CUtensorMap tmAct, tmP;
+int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out, void* xd_out, int64_t M, int64_t C,
+                   int rp, int dtype, float out_scale, float p, uint64_t seed, uint64_t offset, cudaStream_t stream) {
+  CUtensorMap tmAct, tmP, tmXd;
   if (make_tmap(&tmAct, act, dtype, C, M, C, skinny::RP_BK, skinny::RP_BM, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj act")) return 1;
   if (make_tmap(&tmP, P, dtype, C, rp, C, skinny::RP_BK, rp, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj P")) return 1;
+  if (xd_out) {
+    if (make_tmap(&tmXd, xd_out, dtype, C, M, C, skinny::RP_BK, 16, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj Xd")) return 1;
+  } else {
+    tmXd = tmAct;
+  }
   skinny::RowProjParams rp_p;
+  rp_p.store_xd = (xd_out != nullptr && p > 0.f) ? 1 : 0;
   rp_p.out = out;
   rp_p.keep_out = keep_out;
   rp_p.M = (int)M;
@@ -209,7 +215,7 @@ int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out,
   rp_p.offset = offset;
   rp_p.thresh16 = static_cast<uint32_t>(p * 65536.0f + 0.5f);
   const bool bf = dtype == kDtypeBf16;
-#define RP_CASE(BF, RP) return launch_rowproj_t<BF, RP>(tmAct, tmP, rp_p, stream);
+#define RP_CASE(BF, RP) return launch_rowproj_t<BF, RP>(tmAct, tmP, tmXd, rp_p, stream);
   if (bf) {
     if (rp == 16) RP_CASE(true, 16) else if (rp == 32) RP_CASE(true, 32) else RP_CASE(true, 64)
   } else {
@@ -338,7 +344,7 @@ size_t lora_linear_workspace_bytes(int64_t M, int64_t K, int64_t N, int32_t r) {
 }
 
 int lora_linear_fwd(const void* X, const void* W, const void* bias, const float* A, const float* B, void* Y, void* H,
-                    uint8_t* keep_mask, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p,
+                    uint8_t* keep_mask, void* Xd, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p,
                     uint64_t seed, uint64_t offset, int32_t dtype, int32_t w_is_KN, void* workspace,
                     size_t workspace_bytes, cudaStream_t stream) {
   g_err.clear();
@@ -356,7 +362,7 @@ int lora_linear_fwd(const void* X, const void* W, const void* bias, const float*
 
   if (phase_on(kPhasePack) && launch_pack(A, B, ws, w, K, N, r, scaling, dtype, stream)) return 1;
   if (phase_on(kPhaseRowProj) &&
-      launch_rowproj(X, ws + w.a16, H, keep_mask, M, K, rp, dtype, inv_keep, p, seed, offset, stream))
+      launch_rowproj(X, ws + w.a16, H, keep_mask, Xd, M, K, rp, dtype, inv_keep, p, seed, offset, stream))
     return 1;
   if (!phase_on(kPhaseGemm)) return 0;
   GemmArgs g{};
@@ -375,7 +381,7 @@ int lora_linear_fwd(const void* X, const void* W, const void* bias, const float*
 int lora_linear_bwd(const void* dY, const void* X, const void* W, const float* A, const float* B, const void* H,
                     const uint8_t* keep_mask, void* dX, float* dA, float* dB, int64_t M, int64_t K, int64_t N,
                     int32_t r, float scaling, float p, int32_t dtype, int32_t w_is_KN, int32_t accumulate,
-                    void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+                    int32_t x_is_dropped, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
   g_err.clear();
   if (check_common(M, K, N, r, dtype)) return 1;
   if (!dY || !X || !W || !A || !B || !H || !dA || !dB || !workspace) return fail("lora_linear_bwd: null pointer argument");
@@ -394,7 +400,8 @@ int lora_linear_bwd(const void* dY, const void* X, const void* W, const float* A
 
   if (phase_on(kPhasePack) && launch_pack(A, B, ws, w, K, N, r, scaling, dtype, stream)) return 1;
   // dH[M, rp] = dY (sB)
-  if (phase_on(kPhaseRowProj) && launch_rowproj(dY, ws + w.sb16t, dH, nullptr, M, N, rp, dtype, 1.f, 0.f, 0, 0, stream))
+  if (phase_on(kPhaseRowProj) &&
+      launch_rowproj(dY, ws + w.sb16t, dH, nullptr, nullptr, M, N, rp, dtype, 1.f, 0.f, 0, 0, stream))
     return 1;
   if (dX && phase_on(kPhaseGemm)) {
     GemmArgs g{};
@@ -421,7 +428,9 @@ int lora_linear_bwd(const void* dY, const void* X, const void* W, const float* A
   // dB[N, r] = s * dY^T H      (H already carries 1/(1-p))
   if (launch_colproj(dY, H, nullptr, partial, dB, M, N, r, rp, dtype, r, 1, scaling, accumulate, stream)) return 1;
   // dA[r, K] = dH^T drop(X)
-  if (launch_colproj(X, dH, keep, partial, dA, M, K, r, rp, dtype, 1, K, inv_keep, accumulate, stream)) return 1;
+  if (launch_colproj(X, dH, x_is_dropped ? nullptr : keep, partial, dA, M, K, r, rp, dtype, 1, K, inv_keep, accumulate,
+                     stream))
+    return 1;
   return 0;
 }
 

@@ -130,6 +130,7 @@ struct RowProjParams {
   int M, C;
   float out_scale;
   int dropout;  // 0/1
+  int store_xd;  // 1: TMA-store the masked tiles (keep .* Act, unscaled) through tmXd
   uint64_t seed, offset;
   uint32_t thresh16;
 };
@@ -137,7 +138,7 @@ struct RowProjParams {
 template <bool kBf16, int kRPad>
 __global__ void __launch_bounds__(RP_THREADS)
     rowproj_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constant__ CUtensorMap tmP,
-                   const RowProjParams p) {
+                   const __grid_constant__ CUtensorMap tmXd, const RowProjParams p) {
   constexpr int SLOT = rp_slot_bytes<kRPad>();
   constexpr int NB = kRPad / 8;
   extern __shared__ uint8_t smem_raw[];
@@ -189,8 +190,9 @@ __global__ void __launch_bounds__(RP_THREADS)
   const int keep_ld = p.C >> 3;
   uint32_t stage = 0, phase = 0;
   for (int kb = 0; kb < nk; ++kb) {
-    // keep-bits of this warp's 2 chunks per lane: independent of the data, so drawn first
+    // keep-masks of this warp's 2 chunks per lane: independent of the data, so drawn first
     uint32_t bits[2] = {0xFFu, 0xFFu};
+    uint32_t kmask[2][4];
     if (p.dropout) {
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
@@ -198,7 +200,7 @@ __global__ void __launch_bounds__(RP_THREADS)
         const int m = m0 + slab * 16 + (idx >> 3), c = kb * RP_BK + (idx & 7) * 8;
         if (m < p.M && c < p.C) {
           const uint64_t g = (static_cast<uint64_t>(m) * static_cast<uint64_t>(p.C) + static_cast<uint64_t>(c)) >> 3;
-          bits[i] = dropout_keep_bits(g, p.seed, p.offset, p.thresh16);
+          bits[i] = dropout_keep_masks(g, p.seed, p.offset, p.thresh16, kmask[i]);
           p.keep_out[static_cast<size_t>(m) * keep_ld + (c >> 3)] = static_cast<uint8_t>(bits[i]);
         }
       }
@@ -213,10 +215,18 @@ __global__ void __launch_bounds__(RP_THREADS)
         const int R = slab * 16 + (idx >> 3), ch = idx & 7;
         if (bits[i] != 0xFFu) {
           uint4* ptr = reinterpret_cast<uint4*>(act + R * 128 + ((ch ^ (R & 7)) << 4));
-          *ptr = apply_keep(*ptr, bits[i]);
+          uint4 x = *ptr;
+          x.x &= kmask[i][0]; x.y &= kmask[i][1]; x.z &= kmask[i][2]; x.w &= kmask[i][3];
+          *ptr = x;
         }
       }
+      fence_proxy_async_smem();  // in-place writes -> visible to the TMA store / next TMA load
       asm volatile("bar.sync %0, 64;" ::"r"(1 + slab) : "memory");  // the pair's slab is fully masked
+      if (p.store_xd && half == 0 && lane == 0) {
+        // dropout(X) (unscaled) is what backward's dA needs: save it once instead of re-masking X.
+        tma_store_2d(&tmXd, act + slab * 16 * 128, kb * RP_BK, m0 + slab * 16);
+        bulk_commit_group();
+      }
     }
     const uint32_t act_u = smem_u32(act), pt_u = smem_u32(pt);
 #pragma unroll
@@ -237,7 +247,7 @@ __global__ void __launch_bounds__(RP_THREADS)
         mma_16816<kBf16>(acc[n], a, b);
       }
     }
-    if (p.dropout) fence_proxy_async_smem();  // our in-place writes precede the next TMA overwrite
+    if (p.dropout && p.store_xd && half == 0 && lane == 0) bulk_wait_group_read<0>();  // slab read by its store
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[stage]);
     if (++stage == RP_STAGES) {

@@ -59,8 +59,10 @@ class _FusedLoraLinearFn(torch.autograd.Function):
         N = W.shape[1] if w_is_KN else W.shape[0]
         r = A.shape[0]
         ws = _workspace(x.device, binding.workspace_bytes(M, K, N, r))
-        Y, H, keep = binding.linear_fwd(x2, W, bias, A, B, scaling, p, seed, offset, w_is_KN, ws)
-        ctx.save_for_backward(x2, W, A, B, H, keep)
+        Y, H, keep, xd = binding.linear_fwd(x2, W, bias, A, B, scaling, p, seed, offset, w_is_KN, ws, save_xd=True)
+        # With dropout on, backward needs dropout(x) (for dA) and the keep-bits (for dX), not x --
+        # the same tensors torch autograd saves for peft's eager lora_A(dropout(x)).
+        ctx.save_for_backward(xd if xd is not None else x2, W, A, B, H, keep)
         ctx.meta = (scaling, p, w_is_KN, x.shape, N)
         return Y.view(*x.shape[:-1], N)
 
@@ -74,7 +76,8 @@ class _FusedLoraLinearFn(torch.autograd.Function):
         M, K = x2.shape
         ws = _workspace(x2.device, binding.workspace_bytes(M, K, N, A.shape[0]))
         need_dx = ctx.needs_input_grad[0]
-        dX, dA, dB = binding.linear_bwd(dy2, x2, W, A, B, H, keep, scaling, p, w_is_KN, ws, need_dx=need_dx)
+        dX, dA, dB = binding.linear_bwd(dy2, x2, W, A, B, H, keep, scaling, p, w_is_KN, ws, need_dx=need_dx,
+                                        x_is_dropped=keep is not None)
         return (dX.view(x_shape) if need_dx else None, None, None, dA, dB, None, None, None, None, None)
 
 
