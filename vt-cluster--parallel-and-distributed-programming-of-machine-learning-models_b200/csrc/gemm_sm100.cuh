@@ -11,6 +11,8 @@
 //     A1 = dY, B1 = W (other major-ness), p == 0: A2 = dH, B2 = A^T
 //                                         p  > 0: masked epilogue with dh, A^T, keep bits
 //
+// Two launch shapes share this code (template kPair): a lone CTA per 128x256 tile, or a 2-CTA
+// cluster per 256x256 tile driving tcgen05.mma.cta_group::2 (see Cfg below).
 // Roles per CTA (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer
 // (one thread), warp 2 = TMEM allocator, warps 4..7 = epilogue (TMEM -> regs
 // -> swizzled smem -> TMA store).  Two 256-column fp32 accumulators in TMEM
@@ -25,18 +27,27 @@ namespace gemm {
 constexpr int BM = 128;
 constexpr int BN = 256;
 constexpr int BK = 64;  // 64 x 2 B = one 128-byte swizzle row
-constexpr int STAGES = 4;
-constexpr int A_TILE_BYTES = BM * BK * 2;                 // 16 KiB
-constexpr int B_TILE_BYTES = BN * BK * 2;                 // 32 KiB
-constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;  // 48 KiB
+constexpr int A_TILE_BYTES = BM * BK * 2;  // 16 KiB: the CTA's own 128 rows of A1
+// kPair = false: one CTA per 128x256 tile, B tile = 256 rows (32 KiB), 4 stages of 48 KiB.
+// kPair = true : a 2-CTA cluster per 256x256 tile (tcgen05 cta_group::2, UMMA M = 256); each
+//                CTA stages its own 128 rows of A1 and HALF of the B tile (128 rows, 16 KiB),
+//                so L2 -> SMEM traffic per flop halves and 6 stages of 32 KiB fit.
+template <bool kPair>
+struct Cfg {
+  static constexpr int STAGES = kPair ? 6 : 4;
+  static constexpr int B_ROWS = kPair ? BN / 2 : BN;  // rows of the B tile held by one CTA
+  static constexpr int B_TILE_BYTES = B_ROWS * BK * 2;
+  static constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
+  static constexpr int CTAS = kPair ? 2 : 1;
+};
 constexpr int EPI_WARPS = 4;
 constexpr int EPI_BUF_BYTES = 32 * 128;  // 32 rows x 64 cols x 2 B
 constexpr int EPI_BYTES = EPI_WARPS * 2 * EPI_BUF_BYTES;
 constexpr int BAR_BYTES = 256;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;
+constexpr int SMEM_BYTES = 4 * (A_TILE_BYTES + BN * BK * 2) + EPI_BYTES + BAR_BYTES + 1024;  // same for both
 constexpr int THREADS = 256;
 constexpr int TMEM_COLS = 512;
-constexpr int GROUP_M = 16;  // m-blocks per raster group (L2 reuse of B panels)
+constexpr int GROUP_M = 16;  // m-blocks (of one CTA or one pair) per raster group (L2 reuse of B panels)
 
 struct Params {
   int M, N, K1;
@@ -77,13 +88,26 @@ __device__ __forceinline__ void mma_16816_f16(float (&d)[4], const uint32_t (&a)
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
 }
 
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 // kMasked: backward with dropout -- the rank-r term keep/(1-p) .* (dH A) is formed in the
 // epilogue (warp-level MMA + keep-bits) instead of riding the main loop as a K-block.
-template <bool kMasked>
+template <bool kMasked, bool kPair>
 __global__ void __launch_bounds__(THREADS, 1)
     gemm_lora_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                      const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
                      const __grid_constant__ CUtensorMap tmD, const Params p) {
+  using C = Cfg<kPair>;
+  constexpr int STAGES = C::STAGES;
+  constexpr int STAGE_BYTES = C::STAGE_BYTES;
+  constexpr int B_ROWS = C::B_ROWS;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* stage_base = smem;
@@ -97,6 +121,9 @@ __global__ void __launch_bounds__(THREADS, 1)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  // Pair mode: rank 0 is the leader (issues every MMA, owns the full / tmem_empty barriers).
+  const uint32_t cta_rank = kPair ? cluster_ctarank() : 0u;
+  const bool is_leader = cta_rank == 0;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA1);
@@ -109,56 +136,72 @@ __global__ void __launch_bounds__(THREADS, 1)
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < STAGES; ++i) {
-      mbar_init(&full[i], 1);
-      mbar_init(&empty[i], 1);
+      mbar_init(&full[i], C::CTAS);  // pair: leader's expect_tx arrive + the peer's remote arrive
+      mbar_init(&empty[i], 1);       // one (multicast) tcgen05.commit per use
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], EPI_WARPS);
+      mbar_init(&tmem_empty[i], EPI_WARPS * C::CTAS);  // pair: both CTAs' epilogues release it
     }
     fence_barrier_init();
   }
   if (warp == 2) {
-    tmem_alloc(tmem_slot, TMEM_COLS);
-    tmem_relinquish();
+    if constexpr (kPair) {
+      tmem_alloc_2sm(tmem_slot, TMEM_COLS);
+      tmem_relinquish_2sm();
+    } else {
+      tmem_alloc(tmem_slot, TMEM_COLS);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kPair) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int num_m = (p.M + BM - 1) / BM;
+  // Tiles are BM*CTAS rows tall; a cluster (or lone CTA) walks them persistently.
+  constexpr int TILE_M = BM * C::CTAS;
+  const int num_m = (p.M + TILE_M - 1) / TILE_M;
   const int num_n = (p.N + BN - 1) / BN;
   const int num_tiles = num_m * num_n;
   const int nk_main = (p.K1 + BK - 1) / BK;
   const int nk = nk_main + (p.r_pad > 0 ? 1 : 0);
+  const int tile0 = static_cast<int>(blockIdx.x) / C::CTAS;
+  const int tile_step = static_cast<int>(gridDim.x) / C::CTAS;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
-      const uint32_t lora_bytes = static_cast<uint32_t>((BM + BN) * p.r_pad * 2);
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const uint32_t lora_bytes = static_cast<uint32_t>((BM + B_ROWS) * p.r_pad * 2) * C::CTAS;
+      for (int tile = tile0; tile < num_tiles; tile += tile_step) {
         int m_blk, n_blk;
         tile_coords(tile, num_m, num_n, m_blk, n_blk);
+        const int row0 = m_blk * TILE_M + static_cast<int>(cta_rank) * BM;       // this CTA's A rows
+        const int col0 = n_blk * BN + static_cast<int>(cta_rank) * B_ROWS;       // this CTA's slice of B
         for (int kb = 0; kb < nk; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1, 1);
           uint8_t* sa = stage_base + stage * STAGE_BYTES;
           uint8_t* sb = sa + A_TILE_BYTES;
-          if (kb < nk_main) {
-            mbar_arrive_expect_tx(&full[stage], STAGE_BYTES);
-            tma_load_2d(sa, &tmA1, &full[stage], kb * BK, m_blk * BM);
+          const bool main_blk = kb < nk_main;
+          if (is_leader) mbar_arrive_expect_tx(&full[stage], main_blk ? STAGE_BYTES * C::CTAS : lora_bytes);
+          else mbar_arrive_cluster(&full[stage], 0);
+          // In pair mode every load credits the LEADER's barrier (tma_load_2d_2sm).
+          auto load = [&](void* dst, const CUtensorMap* tm, int c0, int c1) {
+            if constexpr (kPair) tma_load_2d_2sm(dst, tm, &full[stage], c0, c1);
+            else tma_load_2d(dst, tm, &full[stage], c0, c1);
+          };
+          if (main_blk) {
+            load(sa, &tmA1, kb * BK, row0);
             if (!p.b_mn_major) {
-              tma_load_2d(sb, &tmB1, &full[stage], kb * BK, n_blk * BN);
+              load(sb, &tmB1, kb * BK, col0);
             } else {
 #pragma unroll
-              for (int j = 0; j < BN / 64; ++j)
-                tma_load_2d(sb + j * (BK * 128), &tmB1, &full[stage], n_blk * BN + j * 64, kb * BK);
+              for (int j = 0; j < B_ROWS / 64; ++j) load(sb + j * (BK * 128), &tmB1, col0 + j * 64, kb * BK);
             }
           } else {
-            mbar_arrive_expect_tx(&full[stage], lora_bytes);
-            tma_load_2d(sa, &tmA2, &full[stage], 0, m_blk * BM);
-            tma_load_2d(sb, &tmB2, &full[stage], 0, n_blk * BN);
+            load(sa, &tmA2, 0, row0);
+            load(sb, &tmB2, 0, col0);
           }
           if (++stage == STAGES) {
             stage = 0;
@@ -170,17 +213,23 @@ __global__ void __launch_bounds__(THREADS, 1)
     __syncwarp();
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    if (lane == 0 && is_leader) {
       const int fmt = (p.dtype == kDtypeBf16) ? 1 : 0;
-      const uint32_t idesc_main = make_idesc_f16(fmt, BM, BN, 0, p.b_mn_major);
-      const uint32_t idesc_lora = make_idesc_f16(fmt, BM, BN, 0, 0);
+      const uint32_t idesc_main = make_idesc_f16(fmt, TILE_M, BN, 0, p.b_mn_major);
+      const uint32_t idesc_lora = make_idesc_f16(fmt, TILE_M, BN, 0, 0);
       const uint32_t lora_sw = static_cast<uint32_t>(p.r_pad) * 2u;  // swizzle span = row bytes
       const uint32_t lora_layout = (lora_sw == 32u) ? 6u : (lora_sw == 64u ? 4u : 2u);
       const uint32_t lora_sbo = 8u * lora_sw;
       const int lora_ksteps = p.r_pad / 16;
+      auto mma = [&](uint32_t d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+        if constexpr (kPair) umma_f16_2sm(d, da, db, idesc, acc); else umma_f16(d, da, db, idesc, acc);
+      };
+      auto commit = [&](uint64_t* bar) {
+        if constexpr (kPair) umma_commit_2sm(bar, 0x3); else umma_commit(bar);  // pair: arrive in both CTAs
+      };
       uint32_t stage = 0, phase = 0;
       uint32_t it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = tile0; tile < num_tiles; tile += tile_step, ++it) {
         const uint32_t buf = it & 1u;
         const uint32_t acc_phase = (it >> 1) & 1u;
         mbar_wait(&tmem_empty[buf], acc_phase ^ 1u, 2);
@@ -197,22 +246,22 @@ __global__ void __launch_bounds__(THREADS, 1)
               const uint64_t da = make_smem_desc(sa + k * 32, 16, 1024, 2);
               const uint64_t db = p.b_mn_major ? make_smem_desc(sb + k * 2048, BK * 128, 1024, 2)
                                                : make_smem_desc(sb + k * 32, 16, 1024, 2);
-              umma_f16(d_tmem, da, db, idesc_main, (kb | k) != 0 ? 1u : 0u);
+              mma(d_tmem, da, db, idesc_main, (kb | k) != 0 ? 1u : 0u);
             }
           } else {
             for (int k = 0; k < lora_ksteps; ++k) {
               const uint64_t da = make_smem_desc(sa + k * 32, 16, lora_sbo, lora_layout);
               const uint64_t db = make_smem_desc(sb + k * 32, 16, lora_sbo, lora_layout);
-              umma_f16(d_tmem, da, db, idesc_lora, 1u);
+              mma(d_tmem, da, db, idesc_lora, 1u);
             }
           }
-          umma_commit(&empty[stage]);  // frees the smem slot once these MMAs retire
+          commit(&empty[stage]);  // frees the smem slot (in both CTAs) once these MMAs retire
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
           }
         }
-        umma_commit(&tmem_full[buf]);  // accumulator complete -> epilogue
+        commit(&tmem_full[buf]);  // accumulator complete -> epilogue (of both CTAs)
       }
     }
     __syncwarp();
@@ -228,12 +277,13 @@ __global__ void __launch_bounds__(THREADS, 1)
     const int dtype = p.dtype;
     const int keep_ld = p.N >> 3;
     const int mk_steps = kMasked ? p.dh_ld / 16 : 0;  // k16 steps of the rank-r product (1, 2 or 4)
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = tile0; tile < num_tiles; tile += tile_step, ++it) {
       int m_blk, n_blk;
       tile_coords(tile, num_m, num_n, m_blk, n_blk);
       const uint32_t buf = it & 1u;
       const uint32_t acc_phase = (it >> 1) & 1u;
-      const int row = m_blk * BM + ew * 32 + lane;
+      const int rbase = m_blk * TILE_M + static_cast<int>(cta_rank) * BM + ew * 32;  // first row of this warp
+      const int row = rbase + lane;
       const bool row_ok = row < p.M;
 
       // dH rows of this warp as mma.sync A-fragments (2 m16 blocks x up to 4 k16 steps),
@@ -245,7 +295,7 @@ __global__ void __launch_bounds__(THREADS, 1)
         for (int mb = 0; mb < 2; ++mb)
 #pragma unroll
           for (int ks = 0; ks < 4; ++ks) {
-            const int r0 = m_blk * BM + ew * 32 + mb * 16 + (lane >> 2);
+            const int r0 = rbase + mb * 16 + (lane >> 2);
             const int k0 = ks * 16 + (lane & 3) * 2;
             const bool ks_ok = ks < mk_steps;
             const size_t o0 = (static_cast<size_t>(r0) * p.dh_ld + k0) >> 1;
@@ -260,7 +310,7 @@ __global__ void __launch_bounds__(THREADS, 1)
       mbar_wait(&tmem_full[buf], acc_phase, 4);
       tc_fence_after();
 
-      const bool warp_rows_ok = m_blk * BM + ew * 32 < p.M;  // else this warp's 32 rows are all padding
+      const bool warp_rows_ok = rbase < p.M;  // else this warp's 32 rows are all padding
       for (int cb = 0; cb < BN / 64 && warp_rows_ok; ++cb) {
         const int col0 = n_blk * BN + cb * 64;
         if (col0 >= p.N) break;  // warp-uniform
@@ -372,7 +422,7 @@ __global__ void __launch_bounds__(THREADS, 1)
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
-          tma_store_2d(&tmD, my_stage + (kMasked ? 0u : sbuf) * EPI_BUF_BYTES, col0, m_blk * BM + ew * 32);
+          tma_store_2d(&tmD, my_stage + (kMasked ? 0u : sbuf) * EPI_BUF_BYTES, col0, rbase);
           bulk_commit_group();
         }
         sbuf ^= 1u;
@@ -380,15 +430,22 @@ __global__ void __launch_bounds__(THREADS, 1)
       // All TMEM reads of this accumulator are done: hand it back to the MMA warp.
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+      if (lane == 0) {
+        if constexpr (kPair) mbar_arrive_cluster(&tmem_empty[buf], 0); else mbar_arrive(&tmem_empty[buf]);
+      }
     }
     if (lane == 0) bulk_wait_group_read<0>();
     __syncwarp();
   }
 
   tc_fence_before();
-  __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem_base, TMEM_COLS);
+  if constexpr (kPair) {
+    cluster_sync_all();  // the peer's smem / TMEM / barriers stay alive until both CTAs are done
+    if (warp == 2) tmem_dealloc_2sm(tmem_base, TMEM_COLS);
+  } else {
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, TMEM_COLS);
+  }
 }
 
 }  // namespace gemm

@@ -6,6 +6,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 
@@ -101,8 +102,10 @@ int device_setup(int* sm_count) {
     CUDA_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
     if (major != 10) return fail("this library contains sm_100a code only; device %d is compute capability %d.x", dev, major);
     CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false>, gemm::SMEM_BYTES));
-    CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<true>, gemm::SMEM_BYTES));
+    CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false, false>, gemm::SMEM_BYTES));
+    CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<true, false>, gemm::SMEM_BYTES));
+    CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false, true>, gemm::SMEM_BYTES));
+    CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<true, true>, gemm::SMEM_BYTES));
 #define OPT_IN_SKINNY(BF, RP)                                                                     \
   CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP>, skinny::rp_smem_bytes<RP>()));             \
   CUDA_TRY(opt_in_smem(skinny::colproj_kernel<BF, RP>, skinny::cp_smem_bytes<RP>()));
@@ -281,18 +284,49 @@ struct GemmArgs {
   float inv_keep;
 };
 
+// LORA_B200_GEMM=1cta forces the single-CTA tile shape (A/B testing); default: CTA pairs whenever
+// the problem has more than one 128-row block.
+bool pair_mode_allowed() {
+  static const bool allowed = [] {
+    const char* e = getenv("LORA_B200_GEMM");
+    return !(e && strcmp(e, "1cta") == 0);
+  }();
+  return allowed;
+}
+
+template <bool kMasked, bool kPair>
+int launch_gemm_t(const CUtensorMap& tmA1, const CUtensorMap& tmB1, const CUtensorMap& tmA2, const CUtensorMap& tmB2,
+                  const CUtensorMap& tmD, const gemm::Params& p, int grid, cudaStream_t stream) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(gemm::THREADS);
+  cfg.dynamicSmemBytes = gemm::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kPair ? 2 : 1;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  CUDA_TRY(cudaLaunchKernelEx(&cfg, gemm::gemm_lora_kernel<kMasked, kPair>, tmA1, tmB1, tmA2, tmB2, tmD, p));
+  return 0;
+}
+
 int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, int sm_count, cudaStream_t stream) {
+  const bool pair = pair_mode_allowed() && M > gemm::BM && sm_count >= 2;
+  const uint32_t b_rows = pair ? gemm::BN / 2 : gemm::BN;  // rows of the B tile one CTA stages
   CUtensorMap tmA1, tmB1, tmA2, tmB2, tmD;
   if (make_tmap(&tmA1, g.A1, dtype, K1, M, K1, gemm::BK, gemm::BM, CU_TENSOR_MAP_SWIZZLE_128B, "gemm A1")) return 1;
   if (!g.b_mn_major) {
-    if (make_tmap(&tmB1, g.B1, dtype, K1, N, K1, gemm::BK, gemm::BN, CU_TENSOR_MAP_SWIZZLE_128B, "gemm B1 (K-major)")) return 1;
+    if (make_tmap(&tmB1, g.B1, dtype, K1, N, K1, gemm::BK, b_rows, CU_TENSOR_MAP_SWIZZLE_128B, "gemm B1 (K-major)")) return 1;
   } else {
     if (make_tmap(&tmB1, g.B1, dtype, N, K1, N, 64, gemm::BK, CU_TENSOR_MAP_SWIZZLE_128B, "gemm B1 (MN-major)")) return 1;
   }
   if (g.rp > 0) {
     const CUtensorMapSwizzle sw = swizzle_for_row_bytes(g.rp * 2);
     if (make_tmap(&tmA2, g.A2, dtype, g.rp, M, g.rp, g.rp, gemm::BM, sw, "gemm A2")) return 1;
-    if (make_tmap(&tmB2, g.B2, dtype, g.rp, N, g.rp, g.rp, gemm::BN, sw, "gemm B2")) return 1;
+    if (make_tmap(&tmB2, g.B2, dtype, g.rp, N, g.rp, g.rp, b_rows, sw, "gemm B2")) return 1;
   } else {
     tmA2 = tmA1;
     tmB2 = tmB1;
@@ -314,14 +348,17 @@ int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, 
   p.keep = g.keep;
   p.inv_keep = g.inv_keep;
 
-  const long long tiles = ((M + gemm::BM - 1) / gemm::BM) * ((N + gemm::BN - 1) / gemm::BN);
+  const int tile_m = pair ? 2 * gemm::BM : gemm::BM;
+  const long long tiles = ((M + tile_m - 1) / tile_m) * ((N + gemm::BN - 1) / gemm::BN);
+  const bool masked = p.masked_r > 0;
+  if (pair) {
+    const int grid = 2 * static_cast<int>(std::min<long long>(tiles, sm_count / 2));
+    return masked ? launch_gemm_t<true, true>(tmA1, tmB1, tmA2, tmB2, tmD, p, grid, stream)
+                  : launch_gemm_t<false, true>(tmA1, tmB1, tmA2, tmB2, tmD, p, grid, stream);
+  }
   const int grid = static_cast<int>(std::min<long long>(tiles, sm_count));
-  if (p.masked_r > 0)
-    gemm::gemm_lora_kernel<true><<<grid, gemm::THREADS, gemm::SMEM_BYTES, stream>>>(tmA1, tmB1, tmA2, tmB2, tmD, p);
-  else
-    gemm::gemm_lora_kernel<false><<<grid, gemm::THREADS, gemm::SMEM_BYTES, stream>>>(tmA1, tmB1, tmA2, tmB2, tmD, p);
-  CUDA_TRY(cudaGetLastError());
-  return 0;
+  return masked ? launch_gemm_t<true, false>(tmA1, tmB1, tmA2, tmB2, tmD, p, grid, stream)
+                : launch_gemm_t<false, false>(tmA1, tmB1, tmA2, tmB2, tmD, p, grid, stream);
 }
 
 __global__ void keep_mask_kernel(uint8_t* keep, long long groups, uint64_t seed, uint64_t offset, uint32_t thresh16) {
