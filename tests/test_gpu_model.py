@@ -1,0 +1,157 @@
+"""Model-level GPU tests: the peft-compatible wrapper over a real HF architecture, driven the way
+the reference drives it (get_peft_model -> model(**batch) -> loss.backward -> AdamW step), against
+the CPU oracle (fp32 torch, oracle/lora_ref.py) with identical weights and tokens.
+
+Per-layer outputs/gradients are held to 2e-2 in test_gpu_parity.py; here errors compound through
+bf16 blocks, so logits/adapter-gradients get 5e-2 and the BASELINE.json criterion "training loss
+after 50 steps within 1 %" is checked directly.  Model-level runs use lora_dropout=0 and HF
+dropouts off: CPU and GPU cannot share torch's own dropout streams (layer-level dropout parity
+with shared Philox masks is in test_gpu_parity.py)."""
+import copy
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import lora_ref
+
+pytestmark = pytest.mark.gpu
+
+
+def relerr(a, ref):
+    a, ref = a.detach().float().cpu(), ref.detach().float().cpu()
+    return float((a - ref).abs().max() / ref.abs().max().clamp_min(1e-20))
+
+
+def _gpt2(n_layer=2, n_embd=256, n_head=4, vocab=512, n_pos=128):
+    from transformers import GPT2Config, GPT2LMHeadModel
+
+    torch.manual_seed(0)
+    cfg = GPT2Config(n_layer=n_layer, n_embd=n_embd, n_head=n_head, vocab_size=vocab, n_positions=n_pos,
+                     resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0)
+    return GPT2LMHeadModel(cfg)
+
+
+def _opt(n_layer=2, hidden=256, ffn=1024, heads=4, vocab=512, n_pos=128):
+    from transformers import OPTConfig, OPTForCausalLM
+
+    torch.manual_seed(0)
+    cfg = OPTConfig(hidden_size=hidden, ffn_dim=ffn, num_hidden_layers=n_layer, num_attention_heads=heads,
+                    word_embed_proj_dim=hidden, vocab_size=vocab, max_position_embeddings=n_pos, dropout=0.0,
+                    attention_dropout=0.0, activation_function="relu", do_layer_norm_before=True)
+    return OPTForCausalLM(cfg)
+
+
+def _pair(pkg, base, targets, r=8, alpha=16, dtype=torch.bfloat16):
+    """(oracle fp32 CPU model, fused bf16 CUDA model) with identical base weights and adapters."""
+    ref = lora_ref.ref_get_peft_model(copy.deepcopy(base), lora_ref.RefLoraConfig(r=r, lora_alpha=alpha,
+                                                                               target_modules=targets))
+    ours = pkg.get_peft_model(copy.deepcopy(base).to(dtype), pkg.LoraConfig(r=r, lora_alpha=alpha,
+                                                                             target_modules=targets, bias="none",
+                                                                             task_type=pkg.TaskType.CAUSAL_LM))
+    # same adapter init on both sides; B random (non-zero) so that every gradient path is exercised
+    g = torch.Generator().manual_seed(7)
+    sd_ref = dict(ref.named_parameters())
+    for n, p in ours.named_parameters():
+        if "lora_" in n:
+            src = sd_ref[n]
+            with torch.no_grad():
+                if "lora_B" in n:
+                    src.copy_(torch.randn(src.shape, generator=g) * 0.02)
+                p.copy_(src)
+    # the 16-bit model sees rounded base weights: give the oracle the same rounded values
+    with torch.no_grad():
+        for (n, p), (_, q) in zip(ref.named_parameters(), ours.named_parameters()):
+            if "lora_" not in n:
+                p.copy_(q.float())
+    return ref, ours.cuda()
+
+
+@pytest.mark.parametrize("arch", ["gpt2", "opt"])
+def test_logits_and_adapter_grads_match_oracle(pkg, arch):
+    base, targets = (_gpt2(), ["c_attn", "c_proj"]) if arch == "gpt2" else (
+        _opt(), ["q_proj", "k_proj", "v_proj", "out_proj", "fc1", "fc2"])
+    ref, ours = _pair(pkg, base, targets)
+    ids = torch.randint(0, 512, (4, 64), generator=torch.Generator().manual_seed(3))
+    ref.train()
+    ours.train()
+    out_r = ref(input_ids=ids).logits
+    loss_r = lora_ref.causal_lm_loss(out_r, ids)
+    loss_r.backward()
+    out_o = ours(input_ids=ids.cuda()).logits
+    loss_o = pkg.train.causal_lm_loss(out_o, ids.cuda())
+    loss_o.backward()
+    assert relerr(out_o, out_r) < 5e-2
+    assert abs(float(loss_o) - float(loss_r)) / float(loss_r) < 1e-2
+    gr = {n: p.grad for n, p in ref.named_parameters() if p.requires_grad}
+    go = {n: p.grad for n, p in ours.named_parameters() if p.requires_grad}
+    assert set(gr) == set(go) and len(gr) > 0
+    worst = max(relerr(go[n], gr[n]) for n in gr)
+    assert worst < 5e-2, worst
+    assert all(p.grad is None for n, p in ours.named_parameters() if "lora_" not in n)  # no dW, no dbias
+
+
+def test_gradient_checkpointing_replays_dropout(pkg):
+    """Both reference scripts enable gradient checkpointing (finetune_lora_distilgpt2.py:93-96):
+    the recomputed forward must redraw the same LoRA-dropout mask, i.e. grads with and without
+    checkpointing are bit-identical for the same seed."""
+    base = _gpt2()
+    cfg = pkg.LoraConfig(r=8, lora_alpha=16, target_modules=["c_attn", "c_proj"], lora_dropout=0.05,
+                         task_type=pkg.TaskType.CAUSAL_LM)
+    ids = torch.randint(0, 512, (2, 64), generator=torch.Generator().manual_seed(5)).cuda()
+    grads = []
+    for ckpt in (False, True):
+        m = copy.deepcopy(base).to(torch.bfloat16)
+        if ckpt:
+            m.gradient_checkpointing_enable()
+        m.config.use_cache = False
+        pm = pkg.get_peft_model(m, cfg).cuda()
+        with torch.no_grad():
+            for n, p in pm.named_parameters():
+                if "lora_B" in n:
+                    p.copy_(torch.randn(p.shape, generator=torch.Generator().manual_seed(11)).to(p.device) * 0.02)
+        pm.train()
+        torch.manual_seed(123)
+        loss = pkg.train.causal_lm_loss(pm(input_ids=ids).logits, ids)
+        loss.backward()
+        grads.append({n: p.grad.clone() for n, p in pm.named_parameters() if p.requires_grad})
+    assert all(g is not None for g in grads[1].values())
+    for n in grads[0]:
+        assert torch.equal(grads[0][n], grads[1][n]), n
+
+
+def test_50_step_loss_within_one_percent(pkg):
+    """BASELINE.json: 'training loss after 50 steps within 1%' of the reference CPU path, same
+    step loop on both sides (AdamW lr 5e-5 -> here 1e-3 so that the loss actually moves, linear
+    decay, clip 1.0), same synthetic tokens."""
+    base = _gpt2(n_layer=2, n_embd=256, n_head=4, vocab=512)
+    ref, ours = _pair(pkg, base, ["c_attn", "c_proj"])
+    batches = pkg.train.synthetic_batches(50, batch=4, seq=64, vocab=512, pad_id=511, seed=1234)
+    losses_ref = lora_ref.train_steps(ref, batches, lr=1e-3, accum=1)
+    tr = pkg.train.Trainer(ours, pkg.train.TrainConfig(lr=1e-3, accum=1))
+    gb = [{k: v.cuda() for k, v in b.items()} for b in batches]
+    losses_ours = [float(l) for l in tr.train(gb)]
+    assert len(losses_ours) == 50
+    assert losses_ref[-1] < losses_ref[0]  # it trains
+    assert abs(losses_ours[-1] - losses_ref[-1]) / losses_ref[-1] < 1e-2, (losses_ours[-1], losses_ref[-1])
+    drift = max(abs(a - b) / b for a, b in zip(losses_ours, losses_ref))
+    assert drift < 2e-2, drift
+
+
+def test_merge_and_disable_paths(pkg):
+    base = _opt()
+    _, ours = _pair(pkg, base, ["q_proj", "v_proj"])
+    ours.eval()
+    ids = torch.randint(0, 512, (2, 32), generator=torch.Generator().manual_seed(9)).cuda()
+    with torch.no_grad():
+        y0 = ours(input_ids=ids).logits.float()
+        ours.merge_adapter()
+        y1 = ours(input_ids=ids).logits.float()
+        ours.unmerge_adapter()
+        ours.disable_adapter_layers()
+        y2 = ours(input_ids=ids).logits.float()
+        ours.enable_adapter_layers()
+        y3 = ours(input_ids=ids).logits.float()
+    assert relerr(y1, y0) < 5e-2  # merged == adapted up to bf16 rounding of W + sBA
+    assert relerr(y3, y0) < 1e-6 or torch.equal(y3, y0)
+    assert relerr(y2, y0) > 1e-4  # disabling the adapters changes the output (B != 0)
