@@ -258,20 +258,46 @@ __host__ __device__ __forceinline__ uint32_t dropout_keep_bits(uint64_t g, uint6
   return bits;
 }
 #ifdef __CUDACC__
-// Same draw, delivered as four AND-masks for the four 32-bit words of a 16-byte chunk of
-// 16-bit elements (0xFFFF per surviving element) plus the packed keep-bits; the per-halfword
-// compares run on the SIMD video path instead of eight scalar compare/select chains.
-__device__ __forceinline__ uint32_t dropout_keep_masks(uint64_t g, uint64_t seed, uint64_t offset, uint32_t thresh16,
+// Round keys of Philox4x32-10 for a fixed seed: hoisted out of the per-group call (the seed is a
+// kernel constant), which removes 20 adds from every draw.
+struct PhiloxKeys {
+  uint32_t k[10][2];
+};
+__device__ __forceinline__ PhiloxKeys philox_round_keys(uint64_t seed) {
+  PhiloxKeys rk;
+  uint32_t k0 = static_cast<uint32_t>(seed), k1 = static_cast<uint32_t>(seed >> 32);
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    rk.k[i][0] = k0;
+    rk.k[i][1] = k1;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  return rk;
+}
+// Same draw as dropout_keep_bits, delivered as four AND-masks for the four 32-bit words of a
+// 16-byte chunk of 16-bit elements (0xFFFF per surviving element) plus the packed keep-bits; the
+// per-halfword compares run on the SIMD video path instead of eight scalar compare/select chains.
+__device__ __forceinline__ uint32_t dropout_keep_masks(uint32_t g_lo, uint32_t g_hi, uint32_t off_lo, uint32_t off_hi,
+                                                       const PhiloxKeys& rk, uint32_t thresh2,
                                                        uint32_t (&mask)[4]) {
-  uint32_t r[4];
-  philox4x32_10(static_cast<uint32_t>(g), static_cast<uint32_t>(g >> 32), static_cast<uint32_t>(offset),
-                static_cast<uint32_t>(offset >> 32), static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32),
-                r);
-  const uint32_t t2 = thresh16 | (thresh16 << 16);
+  uint32_t c0 = g_lo, c1 = g_hi, c2 = off_lo, c3 = off_hi;
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    const uint64_t p0 = static_cast<uint64_t>(0xD2511F53u) * c0;
+    const uint64_t p1 = static_cast<uint64_t>(0xCD9E8D57u) * c2;
+    const uint32_t n0 = static_cast<uint32_t>(p1 >> 32) ^ c1 ^ rk.k[i][0];
+    const uint32_t n2 = static_cast<uint32_t>(p0 >> 32) ^ c3 ^ rk.k[i][1];
+    c1 = static_cast<uint32_t>(p1);
+    c3 = static_cast<uint32_t>(p0);
+    c0 = n0;
+    c2 = n2;
+  }
+  const uint32_t r[4] = {c0, c1, c2, c3};
   uint32_t bits = 0;
 #pragma unroll
   for (int w = 0; w < 4; ++w) {
-    mask[w] = __vcmpgeu2(r[w], t2);  // 0xFFFF where lane >= thresh (unsigned)
+    mask[w] = __vcmpgeu2(r[w], thresh2);  // 0xFFFF where the 16-bit lane >= thresh (unsigned)
     bits |= ((mask[w] & 1u) | ((mask[w] >> 15) & 2u)) << (2 * w);
   }
   return bits;

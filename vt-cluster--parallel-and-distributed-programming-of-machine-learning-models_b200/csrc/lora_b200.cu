@@ -131,7 +131,8 @@ struct Split {
 Split colproj_split(int64_t M, int64_t C) {
   const int64_t c_tiles = (C + skinny::CP_BC - 1) / skinny::CP_BC;
   const int64_t m_tiles = (M + skinny::CP_BM - 1) / skinny::CP_BM;
-  int64_t want = (2 * 148 + c_tiles - 1) / c_tiles;
+  // two CTAs fit per SM: aim for at most one full wave (2*148 CTAs) so that no straggler wave forms
+  int64_t want = (2 * 148) / c_tiles;
   if (want < 1) want = 1;
   if (want > m_tiles) want = m_tiles;
   const int64_t tiles_per = (m_tiles + want - 1) / want;

@@ -188,6 +188,23 @@ __global__ void __launch_bounds__(RP_THREADS)
     for (int e = 0; e < 4; ++e) acc[n][e] = 0.f;
 
   const int keep_ld = p.C >> 3;
+  // Per-lane constants of the dropout draw: the Philox counter of chunk (m, c) is the group index
+  // g = m*(C/8) + c/8, i.e. a per-lane base plus 8 per K-block.
+  PhiloxKeys rk;
+  uint64_t gbase[2] = {0, 0};
+  bool row_ok[2] = {false, false};
+  const uint32_t thresh2 = p.thresh16 | (p.thresh16 << 16);
+  const uint32_t off_lo = static_cast<uint32_t>(p.offset), off_hi = static_cast<uint32_t>(p.offset >> 32);
+  if (p.dropout) {
+    rk = philox_round_keys(p.seed);
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int idx = half * 64 + lane + 32 * i;
+      const int m = m0 + slab * 16 + (idx >> 3);
+      row_ok[i] = m < p.M;
+      gbase[i] = static_cast<uint64_t>(m) * static_cast<uint64_t>(keep_ld) + static_cast<uint64_t>(idx & 7);
+    }
+  }
   uint32_t stage = 0, phase = 0;
   for (int kb = 0; kb < nk; ++kb) {
     // keep-masks of this warp's 2 chunks per lane: independent of the data, so drawn first
@@ -196,12 +213,12 @@ __global__ void __launch_bounds__(RP_THREADS)
     if (p.dropout) {
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
-        const int idx = half * 64 + lane + 32 * i;
-        const int m = m0 + slab * 16 + (idx >> 3), c = kb * RP_BK + (idx & 7) * 8;
-        if (m < p.M && c < p.C) {
-          const uint64_t g = (static_cast<uint64_t>(m) * static_cast<uint64_t>(p.C) + static_cast<uint64_t>(c)) >> 3;
-          bits[i] = dropout_keep_masks(g, p.seed, p.offset, p.thresh16, kmask[i]);
-          p.keep_out[static_cast<size_t>(m) * keep_ld + (c >> 3)] = static_cast<uint8_t>(bits[i]);
+        const int c8 = kb * (RP_BK / 8) + ((half * 64 + lane + 32 * i) & 7);  // chunk column = c/8
+        if (row_ok[i] && c8 < keep_ld) {
+          const uint64_t g = gbase[i] + static_cast<uint64_t>(kb * (RP_BK / 8));
+          bits[i] = dropout_keep_masks(static_cast<uint32_t>(g), static_cast<uint32_t>(g >> 32), off_lo, off_hi, rk,
+                                       thresh2, kmask[i]);
+          p.keep_out[g] = static_cast<uint8_t>(bits[i]);  // byte index == group index
         }
       }
     }
