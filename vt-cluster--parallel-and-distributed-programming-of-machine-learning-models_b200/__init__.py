@@ -7,6 +7,7 @@ on PYTHONPATH so that the reference's `from peft import ...` lines resolve here.
 from . import binding  # noqa: F401  (ctypes C-ABI; fails loudly at first use if the .so is missing)
 from . import lora  # noqa: F401
 from . import train  # noqa: F401
+from . import pipeline  # noqa: F401
 from .api import (  # noqa: F401
     LoraConfig,
     LoraModel,
@@ -21,5 +22,5 @@ from ._build import build  # noqa: F401
 
 __all__ = [
     "LoraConfig", "LoraModel", "PeftModel", "PeftModelForCausalLM", "PeftType", "TaskType", "get_peft_model",
-    "fused_lora_linear", "binding", "lora", "train", "build",
+    "fused_lora_linear", "binding", "lora", "train", "pipeline", "build",
 ]
