@@ -98,6 +98,37 @@ int lora_dropout_keep_mask(uint8_t* keep_mask, int64_t M, int64_t K, float p, ui
                            cudaStream_t stream);
 
 /*
+ * Adapter gradient dB = scaling * dY^T H without any memory handed in or asked for.
+ * No counterpart in the reference.
+ *
+ * For callers that are in no position to allocate device memory or to size a workspace: for
+ * example a plug-in hosted by a runtime whose own pool already owns the GPU's memory (a cudaMalloc
+ * from inside the plug-in may fail, or fragment that pool), or a latency-sensitive loop that must
+ * not hit the driver's allocator (cudaMalloc / cudaFree synchronise the device).  This entry point
+ * calls no cudaMalloc, cudaFree or other allocating routine.  The split partial sums that
+ * lora_linear_bwd keeps in the caller's workspace live here in a block of
+ * LORA_B200_STATIC_SCRATCH_BYTES that is compiled into the library (every GPU that loads the
+ * library holds it until the process exits).  The caller still passes the inputs dY [M,N] and
+ * H [M, lora_linear_rpad(r)] (as written by lora_linear_fwd) and the output dB [N,r] fp32
+ * (overwritten, or added to when accumulate != 0).
+ *
+ *  - Shapes whose partial sums do not fit the block are rejected with an error message that
+ *    states the need and the limit (roughly: row-splits * N * padded-rank * 4 bytes; all the
+ *    reference's shapes at r <= 16 fit).  Use lora_linear_bwd for those.
+ *  - The first call on each device looks up the block's device address (one
+ *    cudaGetSymbolAddress, no allocation); make that first call before starting any stream
+ *    capture on that device.
+ *  - All calls on a device share the one block and it keeps whatever the last call left.  No
+ *    part of it needs clearing (each call overwrites every partial sum it later reads), but two
+ *    calls whose kernels overlap on the GPU (different streams, or different host threads on
+ *    different streams) race on it: keep calls on one stream, or order them with events.
+ *  - Result: bit-identical to the dB that lora_linear_bwd writes for the same dY and H.
+ */
+#define LORA_B200_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
+int lora_linear_grad_b_static(const void* dY, const void* H, float* dB, int64_t M, int64_t N, int32_t r,
+                              float scaling, int32_t dtype, int32_t accumulate, cudaStream_t stream);
+
+/*
  * Profiling hook, no counterpart in the reference: restricts which kernels the
  * calls above launch (bit 0 adapter packing, bit 1 rank-r row projections
  * H/dH, bit 2 the tcgen05 GEMM, bit 3 dA/dB column projections + reduce;

@@ -34,6 +34,8 @@ _SIGNATURES = {
                            c_void_p, c_size_t, c_void_p],
     ),
     "lora_linear_base": (c_int, [c_void_p] * 4 + [c_int64, c_int64, c_int64, c_int32, c_int32, c_void_p]),
+    "lora_linear_grad_b_static": (c_int, [c_void_p] * 3 + [c_int64, c_int64, c_int32, c_float, c_int32, c_int32,
+                                                           c_void_p]),
     "lora_debug_set_phase_mask": (None, [c_int32]),
     "lora_dropout_keep_mask": (c_int, [c_void_p, c_int64, c_int64, c_float, c_uint64, c_uint64, c_void_p]),
 }

@@ -362,6 +362,40 @@ int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, 
                 : launch_gemm_t<false, false>(tmA1, tmB1, tmA2, tmB2, tmD, p, grid, stream);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Scratch for lora_linear_grad_b_static(): a fixed block of device memory that is part of the
+// library image itself, so the entry point never has to ask the driver for memory.  Every GPU
+// that loads the library carries these LORA_B200_STATIC_SCRATCH_BYTES until the process exits.
+// In host code `g_static_scratch` is only a handle for the symbol, not a device address: the
+// real address is looked up once per device with cudaGetSymbolAddress (static_scratch_ptr below)
+// and handed to the kernels as an ordinary pointer.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[LORA_B200_STATIC_SCRATCH_BYTES];
+
+struct StaticScratchSlot {
+  std::atomic<int> ready{0};
+  void* ptr = nullptr;
+};
+StaticScratchSlot g_static_slot[kMaxDevices];
+
+// Device address of g_static_scratch on the CURRENT device; resolved on the first call per device.
+int static_scratch_ptr(void** out) {
+  int dev = 0;
+  CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail("device ordinal %d out of range", dev);
+  StaticScratchSlot& s = g_static_slot[dev];
+  if (!s.ready.load(std::memory_order_acquire)) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      return fail("cudaGetSymbolAddress(static scratch) failed on device %d: %s", dev, cudaGetErrorString(e));
+    s.ptr = p;  // racing first calls resolve the same address; the store order below publishes it
+    s.ready.store(1, std::memory_order_release);
+  }
+  *out = s.ptr;
+  return 0;
+}
+
 __global__ void keep_mask_kernel(uint8_t* keep, long long groups, uint64_t seed, uint64_t offset, uint32_t thresh16) {
   for (long long g = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; g < groups;
        g += static_cast<long long>(gridDim.x) * blockDim.x)
@@ -487,6 +521,29 @@ int lora_linear_base(const void* X, const void* W, const void* bias, void* Y, in
   g.bias = bias;
   g.inv_keep = 1.f;
   return launch_gemm(g, M, N, K, dtype, sms, stream);
+}
+
+int lora_linear_grad_b_static(const void* dY, const void* H, float* dB, int64_t M, int64_t N, int32_t r,
+                               float scaling, int32_t dtype, int32_t accumulate, cudaStream_t stream) {
+  g_err.clear();
+  if (check_common(M, /*K=*/8, N, r, dtype)) return 1;
+  if (!dY || !H || !dB) return fail("lora_linear_grad_b_static: null pointer argument");
+  const int rp = rpad_of(r);
+  const Split sp = colproj_split(M, N);
+  const size_t need = static_cast<size_t>(sp.splits) * static_cast<size_t>(N) * rp * sizeof(float);
+  if (need > static_cast<size_t>(LORA_B200_STATIC_SCRATCH_BYTES))
+    return fail("lora_linear_grad_b_static: this shape needs %zu bytes of partial sums (M=%lld, N=%lld, padded rank %d) "
+                "but the built-in scratch holds %d; use lora_linear_bwd with a caller-provided workspace instead",
+                need, (long long)M, (long long)N, rp, (int)LORA_B200_STATIC_SCRATCH_BYTES);
+  int sms = 0;
+  if (device_setup(&sms)) return 1;
+  void* scratch = nullptr;
+  if (static_scratch_ptr(&scratch)) return 1;
+  // Nothing in the scratch has to start at zero: the column-projection kernel writes every
+  // partial sum of this call (all column tiles of all row splits) before the reduction reads them,
+  // so whatever an earlier call left behind is never observed.
+  return launch_colproj(dY, H, nullptr, static_cast<float*>(scratch), dB, M, N, r, rp, dtype, r, 1, scaling, accumulate,
+                        stream);
 }
 
 void lora_debug_set_phase_mask(int32_t mask) { g_phase_mask.store(mask & kPhaseAll, std::memory_order_relaxed); }
