@@ -227,6 +227,17 @@ __global__ void __launch_bounds__(THREADS, 1)
       auto commit = [&](uint64_t* bar) {
         if constexpr (kPair) umma_commit_2sm(bar, 0x3); else umma_commit(bar);  // pair: arrive in both CTAs
       };
+      // The issuing thread is a serial instruction stream racing a 128-cycle MMA: descriptors are
+      // built once (stage 0, k-step 0) and advanced by adding 16-byte units to their low word
+      // (the 14-bit start-address field cannot overflow: smem is < 256 KiB).
+      const uint32_t smem0 = smem_u32(stage_base);
+      const uint64_t da_main0 = make_smem_desc(smem0, 16, 1024, 2);
+      const uint64_t db_main0 = p.b_mn_major ? make_smem_desc(smem0 + A_TILE_BYTES, BK * 128, 1024, 2)
+                                             : make_smem_desc(smem0 + A_TILE_BYTES, 16, 1024, 2);
+      const uint64_t da_lora0 = make_smem_desc(smem0, 16, lora_sbo, lora_layout);
+      const uint64_t db_lora0 = make_smem_desc(smem0 + A_TILE_BYTES, 16, lora_sbo, lora_layout);
+      const uint32_t b_kstep = p.b_mn_major ? (2048u >> 4) : (32u >> 4);  // K advance of 16 elements
+      constexpr uint32_t kStageUnits = STAGE_BYTES >> 4;
       uint32_t stage = 0, phase = 0;
       uint32_t it = 0;
       for (int tile = tile0; tile < num_tiles; tile += tile_step, ++it) {
@@ -238,22 +249,15 @@ __global__ void __launch_bounds__(THREADS, 1)
         for (int kb = 0; kb < nk; ++kb) {
           mbar_wait(&full[stage], phase, 3);
           tc_fence_after();
-          const uint32_t sa = smem_u32(stage_base + stage * STAGE_BYTES);
-          const uint32_t sb = sa + A_TILE_BYTES;
+          const uint32_t soff = stage * kStageUnits;
           if (kb < nk_main) {
+            const uint64_t da = da_main0 + soff, db = db_main0 + soff;
+            mma(d_tmem, da, db, idesc_main, kb != 0 ? 1u : 0u);
 #pragma unroll
-            for (int k = 0; k < BK / 16; ++k) {
-              const uint64_t da = make_smem_desc(sa + k * 32, 16, 1024, 2);
-              const uint64_t db = p.b_mn_major ? make_smem_desc(sb + k * 2048, BK * 128, 1024, 2)
-                                               : make_smem_desc(sb + k * 32, 16, 1024, 2);
-              mma(d_tmem, da, db, idesc_main, (kb | k) != 0 ? 1u : 0u);
-            }
+            for (uint32_t k = 1; k < BK / 16; ++k) mma(d_tmem, da + k * 2u, db + k * b_kstep, idesc_main, 1u);
           } else {
-            for (int k = 0; k < lora_ksteps; ++k) {
-              const uint64_t da = make_smem_desc(sa + k * 32, 16, lora_sbo, lora_layout);
-              const uint64_t db = make_smem_desc(sb + k * 32, 16, lora_sbo, lora_layout);
-              mma(d_tmem, da, db, idesc_lora, 1u);
-            }
+            const uint64_t da = da_lora0 + soff, db = db_lora0 + soff;
+            for (int k = 0; k < lora_ksteps; ++k) mma(d_tmem, da + k * 2u, db + k * 2u, idesc_lora, 1u);
           }
           commit(&empty[stage]);  // frees the smem slot (in both CTAs) once these MMAs retire
           if (++stage == STAGES) {
@@ -325,6 +329,20 @@ __global__ void __launch_bounds__(THREADS, 1)
           uint32_t v[32];
           tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + buf * BN + cb * 64 + h * 32, v);
           const int c = col0 + h * 32;
+          uint32_t kbits = 0;
+          if constexpr (kMasked) {
+            // keep-bits of this thread's row for the 32 columns: requested now, consumed after the MMA
+            if (row_ok) {
+              const uint8_t* kp = p.keep + static_cast<size_t>(row) * keep_ld + (c >> 3);
+              if (((keep_ld | static_cast<int>(reinterpret_cast<uintptr_t>(p.keep))) & 3) == 0 && c + 32 <= p.N) {
+                kbits = __ldg(reinterpret_cast<const uint32_t*>(kp));
+              } else {
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                  if (c + q * 8 < p.N) kbits |= static_cast<uint32_t>(__ldg(kp + q)) << (8 * q);
+              }
+            }
+          }
           if constexpr (kMasked) {
             // T[32 rows, 32 cols] = dH[32, rp] * A[rp, c..c+31] on the warp's tensor-core path,
             // overlapping the TMEM load above.  B-fragments come from a16t [N, rp] (j contiguous).
@@ -390,13 +408,6 @@ __global__ void __launch_bounds__(THREADS, 1)
             }
           }
           if constexpr (kMasked) {
-            uint32_t kbits = 0;
-            if (row_ok) {
-              const uint8_t* kp = p.keep + static_cast<size_t>(row) * keep_ld + (c >> 3);
-#pragma unroll
-              for (int q = 0; q < 4; ++q)
-                if (c + q * 8 < p.N) kbits |= static_cast<uint32_t>(__ldg(kp + q)) << (8 * q);
-            }
 #pragma unroll
             for (int f = 0; f < 8; ++f) {
               const float4 t4 = *reinterpret_cast<const float4*>(scratch + lane * 32 + ((f ^ (lane & 7)) << 2));
