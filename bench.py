@@ -45,6 +45,13 @@ def parse():
     ap.add_argument("--cpu-tokens", type=int, default=2048, help="tokens per step of the CPU legs (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sweep", action="store_true", help="run the configs[1] shape sweep, one JSON line per point")
+    ap.add_argument("--workload", choices=["layer", "distilgpt2", "opt27b"], default="layer",
+                    help="layer = configs[1] microbench point (default); distilgpt2 / opt27b = whole-model LoRA "
+                         "fine-tune step (configs[2] / configs[3]) through get_peft_model + Trainer (+ DDP)")
+    ap.add_argument("--batch", type=int, default=0, help="model workloads: sequences per GPU per step")
+    ap.add_argument("--seq", type=int, default=0, help="model workloads: sequence length")
+    ap.add_argument("--layers", type=int, default=0, help="model workloads: override the number of layers (debug)")
+    ap.add_argument("--no-ckpt", action="store_true", help="model workloads: gradient checkpointing off")
     return ap.parse_args()
 
 
@@ -312,13 +319,156 @@ def run_point(a, pkg, rank, world, device, emit=True):
     return line
 
 
+# ----------------------------------------------------------------------------------------------
+# whole-model workloads (BASELINE.json configs[2], configs[3]; configs[0] for the CPU arm)
+# ----------------------------------------------------------------------------------------------
+def model_spec(a):
+    """Architecture + LoRA settings of the reference scripts (random init, synthetic tokens)."""
+    if a.workload == "distilgpt2":
+        from transformers import GPT2Config, GPT2LMHeadModel
+
+        cfg = GPT2Config(n_layer=a.layers or 6, n_embd=768, n_head=12, n_positions=1024, vocab_size=50257)
+        targets = ["c_attn", "c_proj"]  # finetune_lora_distilgpt2.py:100
+        return GPT2LMHeadModel, cfg, targets, a.batch or 16, a.seq or 1024, 50256
+    from transformers import OPTConfig, OPTForCausalLM
+
+    cfg = OPTConfig(hidden_size=2560, ffn_dim=10240, num_hidden_layers=a.layers or 32, num_attention_heads=32,
+                    word_embed_proj_dim=2560, vocab_size=50272, max_position_embeddings=2048,
+                    do_layer_norm_before=True, activation_function="relu", dropout=0.1)
+    targets = ["q_proj", "v_proj"]  # BASELINE.json configs[3]
+    return OPTForCausalLM, cfg, targets, a.batch or 4, a.seq or 2048, 1
+
+
+def model_workload_name(a, B, S, world):
+    return (f"{a.workload} architecture (random init) LoRA r=8 alpha=16 dropout=0.05 fine-tune step, "
+            f"gradient checkpointing {'off' if a.no_ckpt else 'on'}, batch {B} x seq {S} per GPU, "
+            f"{'DDP over NCCL, ' if world > 1 else ''}AdamW lr 5e-5 + clip 1.0")
+
+
+def run_model(a, pkg, rank, world, device):
+    import torch.distributed as dist
+
+    cls, cfg, targets, B, S, pad_id = model_spec(a)
+    dtype = torch.bfloat16 if a.dtype == "bf16" else torch.float16
+    torch.manual_seed(0)  # finetune_lora_distilgpt2.py:30
+    with torch.device(device):
+        model = cls(cfg).to(dtype)
+    model.config.use_cache = False
+    if not a.no_ckpt:
+        model.gradient_checkpointing_enable()  # finetune_lora_distilgpt2.py:93-96
+    pm = pkg.get_peft_model(model, pkg.LoraConfig(r=8, lora_alpha=16, target_modules=targets, lora_dropout=0.05,
+                                                  bias="none", task_type=pkg.TaskType.CAUSAL_LM))
+    n_lora = len(pm.base_model.lora_layers())
+    net = pkg.train.wrap_ddp(pm, device) if world > 1 else pm
+    tr = pkg.train.Trainer(net, pkg.train.TrainConfig(lr=5e-5, accum=1, total_steps=10 ** 6))
+    tr._ensure_sched(10 ** 6)
+    net.train()
+    n_batches = 4
+    host = pkg.train.synthetic_batches(n_batches, B, S, cfg.vocab_size, pad_id, seed=1234 + rank)
+    host = [{k: v.pin_memory() for k, v in b.items()} for b in host]
+    dev_batches = [{k: v.to(device) for k, v in b.items()} for b in host]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident(i):
+        loss = tr.micro_step(dev_batches[i % n_batches], sync=True)
+        tr.optimizer_step()
+        return loss
+
+    def step_e2e(i):
+        b = {k: v.to(device, non_blocking=True) for k, v in host[i % n_batches].items()}
+        loss = tr.micro_step(b, sync=True)
+        tr.optimizer_step()
+        return float(loss)  # device -> host read of the step's loss
+
+    def timed(fn, steps, warmup):
+        for i in range(warmup):
+            fn(i)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(torch.cuda.current_device()) as clk:
+            e0.record()
+            for i in range(steps):
+                fn(i)
+            e1.record()
+            barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms / steps, clk
+
+    ms_step, clk = timed(step_resident, a.steps, a.warmup)
+    e2e_ms, _ = timed(step_e2e, max(3, min(a.steps, 10)), 2)
+    tokens = world * B * S
+    fwd_calls = n_lora * (1 if a.no_ckpt else 2)  # checkpointing re-runs every block's forward
+    line = {
+        "metric": "lora_finetune_tokens_per_sec", "value": tokens / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
+        "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
+        "config": {"workload": model_workload_name(a, B, S, world), "global_batch": world * B, "seq_len": S,
+                   "lora_modules": n_lora, "trainable_params": pm.get_nb_trainable_parameters()[0],
+                   "parallelism": f"dp{world}", "l2_policy": "activations + weights far larger than L2"},
+        "clocks": clk.summary(),
+        "e2e": {"value": tokens / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 3 * B * S * 8,
+                "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms},
+        "gpu_launches": a.steps * (fwd_calls * 3 + n_lora * 7),
+    }
+    return line
+
+
+def run_reference_model(a, rank):
+    """CPU arm for the model workloads: BASELINE.json configs[0] -- distilgpt2-architecture LoRA (r=8, c_attn/c_proj)
+    fp32 on the host cores, synthetic tokens seq 128 batch 4 (the reference's own CPU-runnable case); for opt27b a
+    bounded 2-layer slice of the same architecture."""
+    if rank != 0:
+        return
+    from oracle import lora_ref
+
+    a2 = argparse.Namespace(**vars(a))
+    if a.workload == "opt27b":
+        a2.layers = a.layers or 2
+    cls, cfg, targets, _, _, pad_id = model_spec(a2)
+    B, S = 4, 128
+    torch.manual_seed(0)
+    model = cls(cfg)
+    model.config.use_cache = False
+    pm = lora_ref.ref_get_peft_model(model, lora_ref.RefLoraConfig(r=8, lora_alpha=16, target_modules=targets,
+                                                                  lora_dropout=0.05))
+    import __graft_entry__ as g
+
+    pkg = g.load_package()
+    batches = pkg.train.synthetic_batches(max(2, a.steps + 1), B, S, cfg.vocab_size, pad_id, seed=1234)
+    lora_ref.train_steps(pm, batches[:1], lr=5e-5)
+    t0 = time.perf_counter()
+    lora_ref.train_steps(pm, batches[1:1 + a.steps], lr=5e-5)
+    t = (time.perf_counter() - t0) / a.steps
+    v = B * S / t
+    sample = f"batch {B} x seq {S}, {cfg.num_hidden_layers if hasattr(cfg, 'num_hidden_layers') else cfg.n_layer} layers, fp32, {a.steps} steps"
+    print(json.dumps({
+        "impl": "reference", "metric": "lora_finetune_tokens_per_sec", "value": v, "unit": UNIT, "n_gpus": a.gpus,
+        "steps": a.steps, "warmup": a.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{a.workload} architecture LoRA fine-tune step on CPU (configs[0] style)", "sample": sample},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0,
+    }))
+
+
 def main():
     a = parse()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if a.impl == "reference":
-        run_reference(a, rank)
+        if a.workload == "layer":
+            run_reference(a, rank)
+        else:
+            run_reference_model(a, rank)
         return
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the fused LoRA kernels have no CPU fallback "
@@ -335,6 +485,11 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=device)
     try:
+        if a.workload != "layer":
+            line = run_model(a, pkg, rank, world, device)
+            if rank == 0:
+                print(json.dumps(line), flush=True)
+            return
         if a.sweep:
             shapes = [(768, 2304, True), (768, 768, True), (3072, 768, True), (2560, 2560, False),
                       (2560, 10240, False), (10240, 2560, False)]
