@@ -128,8 +128,8 @@ struct Split {
 };
 // Row splits of the column projections; sized for 148 SMs on purpose so that
 // the workspace size does not depend on the device queried.
-Split colproj_split(int64_t M, int64_t C) {
-  const int64_t c_tiles = (C + skinny::CP_BC - 1) / skinny::CP_BC;
+Split colproj_split(int64_t M, int64_t C, int rp) {
+  const int64_t c_tiles = (C + skinny::cp_cols(rp) - 1) / skinny::cp_cols(rp);
   const int64_t m_tiles = (M + skinny::CP_BM - 1) / skinny::CP_BM;
   // two CTAs fit per SM: aim for at most one full wave (2*148 CTAs) so that no straggler wave forms
   int64_t want = (2 * 148) / c_tiles;
@@ -154,7 +154,7 @@ Workspace carve(int64_t M, int64_t K, int64_t N, int r) {
   w.sb16 = off;  off += align256(static_cast<size_t>(rp) * N * 2);
   w.sb16t = off; off += align256(static_cast<size_t>(rp) * N * 2);
   w.dh = off;    off += align256(static_cast<size_t>(M) * rp * 2);
-  const Split sk = colproj_split(M, K), sn = colproj_split(M, N);
+  const Split sk = colproj_split(M, K, rp), sn = colproj_split(M, N, rp);
   const size_t pk = static_cast<size_t>(sk.splits) * K * rp * 4, pn = static_cast<size_t>(sn.splits) * N * rp * 4;
   w.partial = off; off += align256(pk > pn ? pk : pn);
   w.total = off;
@@ -231,7 +231,7 @@ int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out,
 template <bool BF, int RP>
 int launch_colproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmSmall, const skinny::ColProjParams& p, int splits,
                      cudaStream_t stream) {
-  dim3 grid((p.C + skinny::CP_BC - 1) / skinny::CP_BC, splits);
+  dim3 grid((p.C + skinny::cp_cols(RP) - 1) / skinny::cp_cols(RP), splits);
   skinny::colproj_kernel<BF, RP><<<grid, skinny::CP_THREADS, skinny::cp_smem_bytes<RP>(), stream>>>(tmAct, tmSmall, p);
   CUDA_TRY(cudaGetLastError());
   return 0;
@@ -242,9 +242,9 @@ int launch_colproj(const void* act, const void* small, const uint8_t* keep, floa
                    int64_t C, int r, int rp, int dtype, long long ld_c, long long ld_j, float scale, int accumulate,
                    cudaStream_t stream) {
   CUtensorMap tmAct, tmSmall;
-  if (make_tmap(&tmAct, act, dtype, C, M, C, skinny::CP_BC, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_128B, "colproj act")) return 1;
+  if (make_tmap(&tmAct, act, dtype, C, M, C, 64, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_128B, "colproj act")) return 1;
   if (make_tmap(&tmSmall, small, dtype, rp, M, rp, rp, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_NONE, "colproj small")) return 1;
-  const Split sp = colproj_split(M, C);
+  const Split sp = colproj_split(M, C, rp);
   skinny::ColProjParams cp;
   cp.partial = partial;
   cp.keep = keep;
@@ -529,7 +529,7 @@ int lora_linear_grad_b_static(const void* dY, const void* H, float* dB, int64_t 
   if (check_common(M, /*K=*/8, N, r, dtype)) return 1;
   if (!dY || !H || !dB) return fail("lora_linear_grad_b_static: null pointer argument");
   const int rp = rpad_of(r);
-  const Split sp = colproj_split(M, N);
+  const Split sp = colproj_split(M, N, rp);
   const size_t need = static_cast<size_t>(sp.splits) * static_cast<size_t>(N) * rp * sizeof(float);
   if (need > static_cast<size_t>(LORA_B200_STATIC_SCRATCH_BYTES))
     return fail("lora_linear_grad_b_static: this shape needs %zu bytes of partial sums (M=%lld, N=%lld, padded rank %d) "

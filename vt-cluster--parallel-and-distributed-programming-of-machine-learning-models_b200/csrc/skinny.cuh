@@ -111,7 +111,7 @@ __global__ void pack_adapters_kernel(const float* __restrict__ A, const float* _
 // ---------------------------------------------------------------------------
 constexpr int RP_BM = 64;
 constexpr int RP_BK = 64;
-constexpr int RP_STAGES = 6;
+constexpr int RP_STAGES = 5;
 constexpr int RP_ACT_BYTES = RP_BM * 128;  // 8 KiB
 constexpr int RP_CONSUMERS = 8;
 constexpr int RP_THREADS = (RP_CONSUMERS + 1) * 32;
@@ -136,7 +136,7 @@ struct RowProjParams {
 };
 
 template <bool kBf16, int kRPad>
-__global__ void __launch_bounds__(RP_THREADS)
+__global__ void __launch_bounds__(RP_THREADS, (kRPad <= 16 ? 3 : 2))
     rowproj_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constant__ CUtensorMap tmP,
                    const __grid_constant__ CUtensorMap tmXd, const RowProjParams p) {
   constexpr int SLOT = rp_slot_bytes<kRPad>();
@@ -306,23 +306,26 @@ __global__ void __launch_bounds__(RP_THREADS)
 // ---------------------------------------------------------------------------
 // colproj: partial[split][C, kRPad] = sum over the split's rows m of
 //          (keep .* Act)[m, c] * Small[m, j]        (fp32)
-// grid = (ceil(C/64), splits).  Warp 8 is the TMA producer; consumer warp w
-// owns rows 16w..16w+15 of every 128-row tile and all 64 columns; partial sums
-// of the 8 warps meet in shared memory, splits meet in reduce_partials_kernel.
+// grid = (ceil(C / (64*kCB)), splits).  A tile is 128 rows x kCB boxes of 64 columns (each box
+// one 128-byte-swizzled TMA load): kCB = 2 makes every row a 256-byte DRAM segment.  Warp 8 is
+// the TMA producer; consumer warp w owns rows 16w..16w+15 of every tile and all its columns;
+// partial sums of the 8 warps meet in shared memory, splits meet in reduce_partials_kernel.
 // ---------------------------------------------------------------------------
 constexpr int CP_BM = 128;
-constexpr int CP_BC = 64;
-constexpr int CP_STAGES = 4;
-constexpr int CP_ACT_BYTES = CP_BM * 128;  // 16 KiB
+constexpr int CP_BOX_BYTES = CP_BM * 128;  // 16 KiB: 128 rows x 64 columns
 constexpr int CP_CONSUMERS = 8;
 constexpr int CP_THREADS = (CP_CONSUMERS + 1) * 32;
+// 64-column boxes per tile / ring depth, by padded rank (register and smem budget)
+__host__ __device__ constexpr int cp_boxes(int rpad) { return rpad <= 16 ? 2 : 1; }
+__host__ __device__ constexpr int cp_cols(int rpad) { return 64 * cp_boxes(rpad); }
+__host__ __device__ constexpr int cp_stages(int rpad) { return rpad <= 16 ? 3 : 4; }
 template <int kRPad>
 __host__ __device__ constexpr int cp_slot_bytes() {
-  return CP_ACT_BYTES + ((CP_BM * kRPad * 2 + 1023) / 1024) * 1024;
+  return cp_boxes(kRPad) * CP_BOX_BYTES + ((CP_BM * kRPad * 2 + 1023) / 1024) * 1024;
 }
 template <int kRPad>
 __host__ __device__ constexpr int cp_smem_bytes() {
-  return CP_STAGES * cp_slot_bytes<kRPad>() + CP_BC * kRPad * 4 + 1024 + 256;
+  return cp_stages(kRPad) * cp_slot_bytes<kRPad>() + cp_cols(kRPad) * kRPad * 4 + 1024 + 256;
 }
 
 struct ColProjParams {
@@ -339,26 +342,31 @@ __global__ void __launch_bounds__(CP_THREADS)
   constexpr int SLOT = cp_slot_bytes<kRPad>();
   constexpr int NB = kRPad / 8;
   constexpr int SROW = kRPad * 2;  // bytes per row of the Small tile
+  constexpr int kCB = cp_boxes(kRPad);
+  constexpr int COLS = 64 * kCB;
+  constexpr int STAGES = cp_stages(kRPad);
+  constexpr int ACT_BYTES = kCB * CP_BOX_BYTES;
+  constexpr int NCB = 4 * kCB;  // 16-column blocks per tile
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  float* sout = reinterpret_cast<float*>(smem + CP_STAGES * SLOT);
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + CP_STAGES * SLOT + CP_BC * kRPad * 4);
-  uint64_t* empty = full + CP_STAGES;
+  float* sout = reinterpret_cast<float*>(smem + STAGES * SLOT);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * SLOT + COLS * kRPad * 4);
+  uint64_t* empty = full + STAGES;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int c0 = blockIdx.x * CP_BC;
+  const int c0 = blockIdx.x * COLS;
   const int m_begin = blockIdx.y * p.rows_per_split;
   const int m_end = min(p.M, m_begin + p.rows_per_split);
   const int nt = (m_end > m_begin) ? (m_end - m_begin + CP_BM - 1) / CP_BM : 0;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < CP_STAGES; ++i) {
+    for (int i = 0; i < STAGES; ++i) {
       mbar_init(&full[i], 1);
       mbar_init(&empty[i], CP_CONSUMERS);
     }
     fence_barrier_init();
   }
-  for (int i = threadIdx.x; i < CP_BC * kRPad; i += CP_THREADS) sout[i] = 0.f;
+  for (int i = threadIdx.x; i < COLS * kRPad; i += CP_THREADS) sout[i] = 0.f;
   __syncthreads();
 
   if (warp == CP_CONSUMERS) {
@@ -367,10 +375,12 @@ __global__ void __launch_bounds__(CP_THREADS)
       for (int t = 0; t < nt; ++t) {
         mbar_wait(&empty[stage], phase ^ 1, 21);
         uint8_t* act = smem + stage * SLOT;
-        mbar_arrive_expect_tx(&full[stage], CP_ACT_BYTES + CP_BM * SROW);
-        tma_load_2d(act, &tmAct, &full[stage], c0, m_begin + t * CP_BM);
-        tma_load_2d(act + CP_ACT_BYTES, &tmSmall, &full[stage], 0, m_begin + t * CP_BM);
-        if (++stage == CP_STAGES) {
+        mbar_arrive_expect_tx(&full[stage], ACT_BYTES + CP_BM * SROW);
+#pragma unroll
+        for (int bx = 0; bx < kCB; ++bx)
+          tma_load_2d(act + bx * CP_BOX_BYTES, &tmAct, &full[stage], c0 + bx * 64, m_begin + t * CP_BM);
+        tma_load_2d(act + ACT_BYTES, &tmSmall, &full[stage], 0, m_begin + t * CP_BM);
+        if (++stage == STAGES) {
           stage = 0;
           phase ^= 1;
         }
@@ -378,26 +388,29 @@ __global__ void __launch_bounds__(CP_THREADS)
     }
     __syncwarp();
   } else {
-    float acc[4][NB][4];
+    float acc[NCB][NB][4];
 #pragma unroll
-    for (int cbk = 0; cbk < 4; ++cbk)
+    for (int cbk = 0; cbk < NCB; ++cbk)
 #pragma unroll
       for (int n = 0; n < NB; ++n)
 #pragma unroll
         for (int e = 0; e < 4; ++e) acc[cbk][n][e] = 0.f;
 
     const int keep_ld = p.C >> 3;
-    // keep-bytes of this warp's 16 rows x 8 chunks (4 per lane), fetched one tile ahead so the
-    // global-load latency never sits between a tile's arrival and its MMAs.
-    auto load_keep = [&](int mt, uint32_t (&kb)[4]) {
+    // keep-bytes of this warp's 16 rows x (8*kCB) chunks (4*kCB per lane), fetched one tile ahead so
+    // the global-load latency never sits between a tile's arrival and its MMAs.
+    constexpr int NK = 4 * kCB;
+    auto load_keep = [&](int mt, uint32_t (&kb)[NK]) {
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int idx = lane + 32 * i;
-        const int m = mt + warp * 16 + (idx >> 3), c = c0 + (idx & 7) * 8;
+      for (int i = 0; i < NK; ++i) {
+        const int idx = lane + 32 * i;  // chunk id within the warp's slab: row = idx / (8*kCB)
+        const int m = mt + warp * 16 + idx / (8 * kCB), c = c0 + (idx % (8 * kCB)) * 8;
         kb[i] = (m < p.M && c < p.C) ? __ldg(p.keep + static_cast<size_t>(m) * keep_ld + (c >> 3)) : 0xFFu;
       }
     };
-    uint32_t kcur[4] = {0xFFu, 0xFFu, 0xFFu, 0xFFu}, knext[4] = {0xFFu, 0xFFu, 0xFFu, 0xFFu};
+    uint32_t kcur[NK], knext[NK];
+#pragma unroll
+    for (int i = 0; i < NK; ++i) kcur[i] = knext[i] = 0xFFu;
     if (p.keep != nullptr && nt > 0) load_keep(m_begin, kcur);
     uint32_t stage = 0, phase = 0;
     for (int t = 0; t < nt; ++t) {
@@ -407,22 +420,22 @@ __global__ void __launch_bounds__(CP_THREADS)
       uint8_t* act = smem + stage * SLOT;
       if (p.keep != nullptr) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
+        for (int i = 0; i < NK; ++i) {
           const int idx = lane + 32 * i;
-          const int R = warp * 16 + (idx >> 3), ch = idx & 7;
+          const int R = warp * 16 + idx / (8 * kCB), cc = idx % (8 * kCB);  // cc: 16-byte chunk column
           if (kcur[i] != 0xFFu) {
-            uint4* ptr = reinterpret_cast<uint4*>(act + R * 128 + ((ch ^ (R & 7)) << 4));
+            uint4* ptr = reinterpret_cast<uint4*>(act + (cc >> 3) * CP_BOX_BYTES + R * 128 + (((cc & 7) ^ (R & 7)) << 4));
             *ptr = apply_keep(*ptr, kcur[i]);
           }
         }
 #pragma unroll
-        for (int i = 0; i < 4; ++i) kcur[i] = knext[i];
+        for (int i = 0; i < NK; ++i) kcur[i] = knext[i];
         __syncwarp();
       }
       // Rows of the last tile of a split that belong to the next split (or lie
       // beyond M, where TMA filled zeros) must not contribute.
       const int valid_rows = m_end - mt;  // > 0
-      const uint32_t act_u = smem_u32(act), sm_u = act_u + CP_ACT_BYTES;
+      const uint32_t act_u = smem_u32(act), sm_u = act_u + ACT_BYTES;
       const bool warp_live = warp * 16 < valid_rows;
       if (warp_live) {
         uint32_t b[NB][2];
@@ -446,12 +459,12 @@ __global__ void __launch_bounds__(CP_THREADS)
             }
         }
 #pragma unroll
-        for (int cbk = 0; cbk < 4; ++cbk) {
+        for (int cbk = 0; cbk < NCB; ++cbk) {
           uint32_t a[4];
           const int q = lane >> 3, i = lane & 7;
           const int mrow = warp * 16 + (q >> 1) * 8 + i;
-          const int ch = cbk * 2 + (q & 1);
-          ldsm_x4_t(act_u + mrow * 128 + ((ch ^ (mrow & 7)) << 4), a);
+          const int ch = (cbk & 3) * 2 + (q & 1);
+          ldsm_x4_t(act_u + (cbk >> 2) * CP_BOX_BYTES + mrow * 128 + ((ch ^ (mrow & 7)) << 4), a);
 #pragma unroll
           for (int n = 0; n < NB; ++n) mma_16816<kBf16>(acc[cbk][n], a, b[n]);
         }
@@ -459,7 +472,7 @@ __global__ void __launch_bounds__(CP_THREADS)
       if (p.keep != nullptr) fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[stage]);
-      if (++stage == CP_STAGES) {
+      if (++stage == STAGES) {
         stage = 0;
         phase ^= 1;
       }
@@ -471,7 +484,7 @@ __global__ void __launch_bounds__(CP_THREADS)
     for (int turn = 0; turn < CP_CONSUMERS; ++turn) {
       if (warp == turn) {
 #pragma unroll
-        for (int cbk = 0; cbk < 4; ++cbk)
+        for (int cbk = 0; cbk < NCB; ++cbk)
 #pragma unroll
           for (int n = 0; n < NB; ++n)
 #pragma unroll
@@ -486,7 +499,7 @@ __global__ void __launch_bounds__(CP_THREADS)
   }
   __syncthreads();
   float* dst = p.partial + (static_cast<size_t>(blockIdx.y) * p.C + c0) * kRPad;
-  const int ncols = min(CP_BC, p.C - c0);
+  const int ncols = min(COLS, p.C - c0);
   for (int i = threadIdx.x; i < ncols * kRPad; i += CP_THREADS) dst[i] = sout[i];
 }
 
