@@ -329,7 +329,7 @@ def run_point(a, pkg, rank, world, device, with_e2e=True):
                                 ((3 * M * K + 2 * M * N + K * N) * 2 / 1e6 if K == N else
                                  (2 * M * K + 2 * M * N + K * N) * 2 / 1e6),
                    "exchange": "NCCL all-reduce(avg) of the flat adapter-grad bucket every step, overlapped with the next step's compute (two buckets)" if dist_on else "none"},
-        "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 10 * a.steps, "roofline": roofline,
+        "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 7 * a.steps,  # fwd: pack, rowproj, gemm; bwd: pack, rowproj, gemm, colproj(dB+dA, reduction folded in) "roofline": roofline,
     }
     return line
 
@@ -431,7 +431,7 @@ def run_model(a, pkg, rank, world, device):
         "clocks": clk.summary(),
         "e2e": {"value": tokens / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 3 * B * S * 8,
                 "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms},
-        "gpu_launches": a.steps * (fwd_calls * 3 + n_lora * 7),
+        "gpu_launches": a.steps * (fwd_calls * 3 + n_lora * 4),
     }
     return line
 

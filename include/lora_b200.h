@@ -118,10 +118,13 @@ int lora_dropout_keep_mask(uint8_t* keep_mask, int64_t M, int64_t K, float p, ui
  *  - The first call on each device looks up the block's device address (one
  *    cudaGetSymbolAddress, no allocation); make that first call before starting any stream
  *    capture on that device.
- *  - All calls on a device share the one block and it keeps whatever the last call left.  No
- *    part of it needs clearing (each call overwrites every partial sum it later reads), but two
- *    calls whose kernels overlap on the GPU (different streams, or different host threads on
- *    different streams) race on it: keep calls on one stream, or order them with events.
+ *  - All calls on a device share the one block and it keeps whatever the last call left.  The
+ *    only part that must start at zero -- a small table of arrival counters at its head -- is
+ *    zero when the library loads and is left at zero by every completed call; the partial sums
+ *    need no clearing (each call overwrites every one it later reads).  Two calls whose kernels
+ *    overlap on the GPU (different streams, or different host threads on different streams)
+ *    race on the block: keep calls on one stream, or order them with events.  A call that is
+ *    aborted mid-kernel (device reset, trap) may leave counters non-zero: reload the library.
  *  - Result: bit-identical to the dB that lora_linear_bwd writes for the same dY and H.
  */
 #define LORA_B200_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)

@@ -3,6 +3,7 @@
 // sequencing.  Replaces the peft lora.Linear forward and its autograd backward
 // that the reference reaches through get_peft_model
 // (finetune_lora_distilgpt2.py:98-104, finetune_lora_opt_pp.py:104-112).
+#include <algorithm>
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
@@ -142,8 +143,9 @@ Split colproj_split(int64_t M, int64_t C, int rp) {
   return s;
 }
 
+constexpr int kMaxColTiles = 4096;  // arrival counters per column projection (C <= 4096*64 columns)
 struct Workspace {
-  size_t a16, a16t, sb16, sb16t, dh, partial, total;
+  size_t a16, a16t, sb16, sb16t, dh, counters, partial, partial2, total;
 };
 Workspace carve(int64_t M, int64_t K, int64_t N, int r) {
   const int rp = rpad_of(r);
@@ -154,9 +156,11 @@ Workspace carve(int64_t M, int64_t K, int64_t N, int r) {
   w.sb16 = off;  off += align256(static_cast<size_t>(rp) * N * 2);
   w.sb16t = off; off += align256(static_cast<size_t>(rp) * N * 2);
   w.dh = off;    off += align256(static_cast<size_t>(M) * rp * 2);
+  w.counters = off; off += align256(2 * kMaxColTiles * sizeof(unsigned int));
   const Split sk = colproj_split(M, K, rp), sn = colproj_split(M, N, rp);
   const size_t pk = static_cast<size_t>(sk.splits) * K * rp * 4, pn = static_cast<size_t>(sn.splits) * N * rp * 4;
-  w.partial = off; off += align256(pk > pn ? pk : pn);
+  w.partial = off;  off += align256(pn);   // dB partial sums
+  w.partial2 = off; off += align256(pk);   // dA partial sums (both column projections share one launch)
   w.total = off;
   return w;
 }
@@ -178,11 +182,12 @@ int launch_pack(const float* A, const float* B, uint8_t* ws, const Workspace& w,
   if (dtype == kDtypeBf16)
     skinny::pack_adapters_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(
         A, B, (__nv_bfloat16*)(ws + w.a16), (__nv_bfloat16*)(ws + w.a16t), (__nv_bfloat16*)(ws + w.sb16),
-        (__nv_bfloat16*)(ws + w.sb16t), (int)K, (int)N, r, rp, s);
+        (__nv_bfloat16*)(ws + w.sb16t), (int)K, (int)N, r, rp, s, (unsigned int*)(ws + w.counters), 2 * kMaxColTiles);
   else
     skinny::pack_adapters_kernel<__half><<<grid, 256, 0, stream>>>(A, B, (__half*)(ws + w.a16), (__half*)(ws + w.a16t),
                                                                     (__half*)(ws + w.sb16), (__half*)(ws + w.sb16t),
-                                                                    (int)K, (int)N, r, rp, s);
+                                                                    (int)K, (int)N, r, rp, s,
+                                                                    (unsigned int*)(ws + w.counters), 2 * kMaxColTiles);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -228,45 +233,70 @@ int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out,
 #undef RP_CASE
 }
 
+// One column projection: out[c*ld_c + j*ld_j] (=|+=) scale * sum_m keep(m,c) act[m,c] small[m,j],  c < C, j < r
+struct ColProjJob {
+  const void* act;
+  const void* small;
+  const uint8_t* keep;
+  float* partial;
+  unsigned int* counters;
+  float* out;
+  int64_t C;
+  long long ld_c, ld_j;
+  float scale;
+};
+
 template <bool BF, int RP>
-int launch_colproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmSmall, const skinny::ColProjParams& p, int splits,
-                     cudaStream_t stream) {
-  dim3 grid((p.C + skinny::cp_cols(RP) - 1) / skinny::cp_cols(RP), splits);
-  skinny::colproj_kernel<BF, RP><<<grid, skinny::CP_THREADS, skinny::cp_smem_bytes<RP>(), stream>>>(tmAct, tmSmall, p);
+int launch_colproj_t(const CUtensorMap (&tmAct)[2], const CUtensorMap (&tmSmall)[2], const skinny::ColProjParams& pp,
+                     int njobs, cudaStream_t stream) {
+  int gx = 0, gy = 0;
+  for (int i = 0; i < njobs; ++i) {
+    gx = std::max(gx, pp.prob[i].c_tiles);
+    gy = std::max(gy, pp.prob[i].splits);
+  }
+  dim3 grid(gx, gy, njobs);
+  skinny::colproj_kernel<BF, RP><<<grid, skinny::CP_THREADS, skinny::cp_smem_bytes<RP>(), stream>>>(
+      tmAct[0], tmSmall[0], tmAct[1], tmSmall[1], pp);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
 
-// out[c*ld_c + j*ld_j] (=|+=) scale * sum_m keep(m,c) act[m,c] small[m,j],  c < C, j < r
-int launch_colproj(const void* act, const void* small, const uint8_t* keep, float* partial, float* out, int64_t M,
-                   int64_t C, int r, int rp, int dtype, long long ld_c, long long ld_j, float scale, int accumulate,
+// Up to two column projections over the same M rows in ONE launch; each folds its own row splits
+// (last CTA per column tile), so no reduction kernel follows.
+int launch_colproj(const ColProjJob* jobs, int njobs, int64_t M, int r, int rp, int dtype, int accumulate,
                    cudaStream_t stream) {
-  CUtensorMap tmAct, tmSmall;
-  if (make_tmap(&tmAct, act, dtype, C, M, C, 64, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_128B, "colproj act")) return 1;
-  if (make_tmap(&tmSmall, small, dtype, rp, M, rp, rp, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_NONE, "colproj small")) return 1;
-  const Split sp = colproj_split(M, C, rp);
-  skinny::ColProjParams cp;
-  cp.partial = partial;
-  cp.keep = keep;
-  cp.M = (int)M;
-  cp.C = (int)C;
-  cp.rows_per_split = sp.rows_per_split;
+  CUtensorMap tmAct[2], tmSmall[2];
+  skinny::ColProjParams pp{};
+  for (int i = 0; i < 2; ++i) {
+    const ColProjJob& j = jobs[i < njobs ? i : 0];
+    if (make_tmap(&tmAct[i], j.act, dtype, j.C, M, j.C, 64, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_128B, "colproj act")) return 1;
+    if (make_tmap(&tmSmall[i], j.small, dtype, rp, M, rp, rp, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_NONE, "colproj small")) return 1;
+    const Split sp = colproj_split(M, j.C, rp);
+    skinny::ColProjProblem& q = pp.prob[i];
+    q.partial = j.partial;
+    q.counters = j.counters;
+    q.keep = j.keep;
+    q.out = j.out;
+    q.ld_c = j.ld_c;
+    q.ld_j = j.ld_j;
+    q.scale = j.scale;
+    q.accumulate = accumulate;
+    q.r = r;
+    q.M = (int)M;
+    q.C = (int)j.C;
+    q.rows_per_split = sp.rows_per_split;
+    q.splits = sp.splits;
+    q.c_tiles = static_cast<int>((j.C + skinny::cp_cols(rp) - 1) / skinny::cp_cols(rp));
+    if (q.c_tiles > kMaxColTiles) return fail("column projection over %lld columns exceeds the %d-tile counter table", (long long)j.C, kMaxColTiles);
+  }
   const bool bf = dtype == kDtypeBf16;
-  int rc;
-#define CP_CASE(BF, RP) rc = launch_colproj_t<BF, RP>(tmAct, tmSmall, cp, sp.splits, stream);
+#define CP_CASE(BF, RP) return launch_colproj_t<BF, RP>(tmAct, tmSmall, pp, njobs, stream);
   if (bf) {
     if (rp == 16) CP_CASE(true, 16) else if (rp == 32) CP_CASE(true, 32) else CP_CASE(true, 64)
   } else {
     if (rp == 16) CP_CASE(false, 16) else if (rp == 32) CP_CASE(false, 32) else CP_CASE(false, 64)
   }
 #undef CP_CASE
-  if (rc) return rc;
-  const long long total = static_cast<long long>(C) * r;
-  const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, 1024));
-  skinny::reduce_partials_kernel<<<grid, 256, 0, stream>>>(partial, out, sp.splits, (int)C, rp, r, ld_c, ld_j, scale,
-                                                           accumulate);
-  CUDA_TRY(cudaGetLastError());
-  return 0;
 }
 
 struct GemmArgs {
@@ -497,13 +527,13 @@ int lora_linear_bwd(const void* dY, const void* X, const void* W, const float* A
     // launch_gemm derives dh_ld from rp/masked_r; both give rp here.
   }
   if (!phase_on(kPhaseColProj)) return 0;
-  // dB[N, r] = s * dY^T H      (H already carries 1/(1-p))
-  if (launch_colproj(dY, H, nullptr, partial, dB, M, N, r, rp, dtype, r, 1, scaling, accumulate, stream)) return 1;
-  // dA[r, K] = dH^T drop(X)
-  if (launch_colproj(X, dH, x_is_dropped ? nullptr : keep, partial, dA, M, K, r, rp, dtype, 1, K, inv_keep, accumulate,
-                     stream))
-    return 1;
-  return 0;
+  // dB[N, r] = s * dY^T H (H already carries 1/(1-p))  and  dA[r, K] = dH^T drop(X), one launch
+  unsigned int* counters = reinterpret_cast<unsigned int*>(ws + w.counters);
+  ColProjJob jobs[2];
+  jobs[0] = ColProjJob{dY, H, nullptr, partial, counters, dB, N, (long long)r, 1ll, scaling};
+  jobs[1] = ColProjJob{X, dH, x_is_dropped ? nullptr : keep, reinterpret_cast<float*>(ws + w.partial2),
+                       counters + kMaxColTiles, dA, K, 1ll, (long long)K, inv_keep};
+  return launch_colproj(jobs, 2, M, r, rp, dtype, accumulate, stream);
 }
 
 int lora_linear_base(const void* X, const void* W, const void* bias, void* Y, int64_t M, int64_t K, int64_t N,
@@ -530,7 +560,8 @@ int lora_linear_grad_b_static(const void* dY, const void* H, float* dB, int64_t 
   if (!dY || !H || !dB) return fail("lora_linear_grad_b_static: null pointer argument");
   const int rp = rpad_of(r);
   const Split sp = colproj_split(M, N, rp);
-  const size_t need = static_cast<size_t>(sp.splits) * static_cast<size_t>(N) * rp * sizeof(float);
+  const size_t counter_bytes = align256(kMaxColTiles * sizeof(unsigned int));
+  const size_t need = counter_bytes + static_cast<size_t>(sp.splits) * static_cast<size_t>(N) * rp * sizeof(float);
   if (need > static_cast<size_t>(LORA_B200_STATIC_SCRATCH_BYTES))
     return fail("lora_linear_grad_b_static: this shape needs %zu bytes of partial sums (M=%lld, N=%lld, padded rank %d) "
                 "but the built-in scratch holds %d; use lora_linear_bwd with a caller-provided workspace instead",
@@ -539,11 +570,13 @@ int lora_linear_grad_b_static(const void* dY, const void* H, float* dB, int64_t 
   if (device_setup(&sms)) return 1;
   void* scratch = nullptr;
   if (static_scratch_ptr(&scratch)) return 1;
-  // Nothing in the scratch has to start at zero: the column-projection kernel writes every
-  // partial sum of this call (all column tiles of all row splits) before the reduction reads them,
-  // so whatever an earlier call left behind is never observed.
-  return launch_colproj(dY, H, nullptr, static_cast<float*>(scratch), dB, M, N, r, rp, dtype, r, 1, scaling, accumulate,
-                        stream);
+  // What must start at zero are the arrival counters at the head of the block: they are zero when
+  // the library is loaded and every call leaves them at zero again (each counter wraps after the
+  // last row split of its column tile has arrived).  The partial sums behind them need no clearing:
+  // every one that is read was written earlier in the same call.
+  ColProjJob job{dY, H, nullptr, reinterpret_cast<float*>(static_cast<unsigned char*>(scratch) + counter_bytes),
+                 static_cast<unsigned int*>(scratch), dB, N, (long long)r, 1ll, scaling};
+  return launch_colproj(&job, 1, M, r, rp, dtype, accumulate, stream);
 }
 
 void lora_debug_set_phase_mask(int32_t mask) { g_phase_mask.store(mask & kPhaseAll, std::memory_order_relaxed); }

@@ -64,7 +64,8 @@ __device__ __forceinline__ uint4 apply_keep(uint4 x, uint32_t bits) {
 
 // ---------------------------------------------------------------------------
 // pack: fp32 masters A[r,K], B[N,r] -> 16-bit operands in the four layouts the
-// kernels read (zero padded to r_pad; the scaling s is folded into B).
+// kernels read (zero padded to r_pad; the scaling s is folded into B); also clears
+// the arrival counters of the column projections that follow in the same call.
 //   a16 [r_pad,K]   a16t [K,r_pad]   sb16 [N,r_pad]   sb16t [r_pad,N]
 // ---------------------------------------------------------------------------
 template <typename T>
@@ -81,7 +82,9 @@ __device__ __forceinline__ __half cvt16<__half>(float v) {
 template <typename T>
 __global__ void pack_adapters_kernel(const float* __restrict__ A, const float* __restrict__ B, T* __restrict__ a16,
                                      T* __restrict__ a16t, T* __restrict__ sb16, T* __restrict__ sb16t, int K, int N,
-                                     int r, int r_pad, float s) {
+                                     int r, int r_pad, float s, unsigned int* __restrict__ counters, int n_counters) {
+  // the column-projection kernels of the same call count arrivals here (must start at zero)
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_counters; i += gridDim.x * blockDim.x) counters[i] = 0u;
   const long long na = static_cast<long long>(r_pad) * K;
   const long long nb = static_cast<long long>(N) * r_pad;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < na + nb;
@@ -328,17 +331,33 @@ __host__ __device__ constexpr int cp_smem_bytes() {
   return cp_stages(kRPad) * cp_slot_bytes<kRPad>() + cp_cols(kRPad) * kRPad * 4 + 1024 + 256;
 }
 
-struct ColProjParams {
-  float* partial;       // [splits][C][kRPad]
-  const uint8_t* keep;  // [M, C/8] or null
+struct ColProjProblem {
+  float* partial;          // [splits][C][kRPad] split partial sums (scratch)
+  unsigned int* counters;  // [c_tiles], zero on entry; self-resetting (atomicInc wraps)
+  const uint8_t* keep;     // [M, C/8] or null
+  float* out;              // out[c*ld_c + j*ld_j], j < r
+  long long ld_c, ld_j;
+  float scale;
+  int accumulate;
+  int r;
   int M, C;
   int rows_per_split;  // multiple of CP_BM
+  int splits, c_tiles;
+};
+// One launch carries up to two independent problems (dB and dA of one backward): blockIdx.z.
+struct ColProjParams {
+  ColProjProblem prob[2];
 };
 
 template <bool kBf16, int kRPad>
 __global__ void __launch_bounds__(CP_THREADS)
-    colproj_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constant__ CUtensorMap tmSmall,
-                   const ColProjParams p) {
+    colproj_kernel(const __grid_constant__ CUtensorMap tmAct0, const __grid_constant__ CUtensorMap tmSmall0,
+                   const __grid_constant__ CUtensorMap tmAct1, const __grid_constant__ CUtensorMap tmSmall1,
+                   const ColProjParams pp) {
+  const ColProjProblem& p = pp.prob[blockIdx.z];
+  if (static_cast<int>(blockIdx.x) >= p.c_tiles || static_cast<int>(blockIdx.y) >= p.splits) return;  // CTA-uniform
+  const CUtensorMap* tmAct = blockIdx.z == 0 ? &tmAct0 : &tmAct1;
+  const CUtensorMap* tmSmall = blockIdx.z == 0 ? &tmSmall0 : &tmSmall1;
   constexpr int SLOT = cp_slot_bytes<kRPad>();
   constexpr int NB = kRPad / 8;
   constexpr int SROW = kRPad * 2;  // bytes per row of the Small tile
@@ -378,8 +397,8 @@ __global__ void __launch_bounds__(CP_THREADS)
         mbar_arrive_expect_tx(&full[stage], ACT_BYTES + CP_BM * SROW);
 #pragma unroll
         for (int bx = 0; bx < kCB; ++bx)
-          tma_load_2d(act + bx * CP_BOX_BYTES, &tmAct, &full[stage], c0 + bx * 64, m_begin + t * CP_BM);
-        tma_load_2d(act + ACT_BYTES, &tmSmall, &full[stage], 0, m_begin + t * CP_BM);
+          tma_load_2d(act + bx * CP_BOX_BYTES, tmAct, &full[stage], c0 + bx * 64, m_begin + t * CP_BM);
+        tma_load_2d(act + ACT_BYTES, tmSmall, &full[stage], 0, m_begin + t * CP_BM);
         if (++stage == STAGES) {
           stage = 0;
           phase ^= 1;
@@ -501,6 +520,29 @@ __global__ void __launch_bounds__(CP_THREADS)
   float* dst = p.partial + (static_cast<size_t>(blockIdx.y) * p.C + c0) * kRPad;
   const int ncols = min(COLS, p.C - c0);
   for (int i = threadIdx.x; i < ncols * kRPad; i += CP_THREADS) dst[i] = sout[i];
+
+  // The last CTA of this column tile to finish folds the splits, always in split order 0,1,2,...
+  // (the arrival order only decides WHO adds, never the order of the additions), applies the
+  // scale and writes the gradient: no separate reduction launch.
+  __shared__ int s_is_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int prev = atomicInc(p.counters + blockIdx.x, static_cast<unsigned int>(p.splits - 1));
+    s_is_last = (prev == static_cast<unsigned int>(p.splits - 1));
+  }
+  __syncthreads();
+  if (s_is_last) {
+    __threadfence();
+    for (int i = threadIdx.x; i < ncols * p.r; i += CP_THREADS) {
+      const int cl = i / p.r, j = i - cl * p.r;
+      const float* src = p.partial + static_cast<size_t>(c0 + cl) * kRPad + j;
+      float acc = 0.f;
+      for (int sp = 0; sp < p.splits; ++sp) acc += __ldcg(src + static_cast<size_t>(sp) * p.C * kRPad);
+      float* o = p.out + static_cast<long long>(c0 + cl) * p.ld_c + static_cast<long long>(j) * p.ld_j;
+      *o = p.accumulate ? (*o + p.scale * acc) : (p.scale * acc);
+    }
+  }
 }
 
 // out[c*ld_c + j*ld_j] = scale * sum_split partial[split][c][j]  (+ old if accumulate), j < r
