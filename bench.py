@@ -319,6 +319,7 @@ def run_point(a, pkg, rank, world, device, with_e2e=True):
         e2e = {"value": world * M / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": (M * K + M * N) * esz,
                "d2h_bytes_per_step": (M * N + M * K) * esz + (r * K + N * r) * 4, "ms_per_step": e2e_ms}
 
+    # launches per step: fwd pack, rowproj, gemm; bwd pack, rowproj, gemm, colproj (dB+dA, reduction folded in)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -329,7 +330,7 @@ def run_point(a, pkg, rank, world, device, with_e2e=True):
                                 ((3 * M * K + 2 * M * N + K * N) * 2 / 1e6 if K == N else
                                  (2 * M * K + 2 * M * N + K * N) * 2 / 1e6),
                    "exchange": "NCCL all-reduce(avg) of the flat adapter-grad bucket every step, overlapped with the next step's compute (two buckets)" if dist_on else "none"},
-        "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 7 * a.steps,  # fwd: pack, rowproj, gemm; bwd: pack, rowproj, gemm, colproj(dB+dA, reduction folded in) "roofline": roofline,
+        "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 7 * a.steps, "roofline": roofline,
     }
     return line
 

@@ -125,7 +125,8 @@ int lora_dropout_keep_mask(uint8_t* keep_mask, int64_t M, int64_t K, float p, ui
  *    overlap on the GPU (different streams, or different host threads on different streams)
  *    race on the block: keep calls on one stream, or order them with events.  A call that is
  *    aborted mid-kernel (device reset, trap) may leave counters non-zero: reload the library.
- *  - Result: bit-identical to the dB that lora_linear_bwd writes for the same dY and H.
+ *  - Result: the dB that lora_linear_bwd writes for the same dY and H, up to fp32 rounding
+ *    (the two paths may cut the rows into a different number of partial sums).
  */
 #define LORA_B200_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
 int lora_linear_grad_b_static(const void* dY, const void* H, float* dB, int64_t M, int64_t N, int32_t r,

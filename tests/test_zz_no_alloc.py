@@ -18,7 +18,7 @@ import torch
 
 pytestmark = pytest.mark.gpu
 
-TOL = 2e-2  # same bound as tests/test_gpu_parity.py (in practice the two paths agree bit for bit)
+TOL = 2e-2  # same bound as tests/test_gpu_parity.py (in practice the two paths differ by fp32 rounding only)
 
 
 def _relerr(a, ref):

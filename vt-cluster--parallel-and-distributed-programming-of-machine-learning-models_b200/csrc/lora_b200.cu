@@ -129,11 +129,11 @@ struct Split {
 };
 // Row splits of the column projections; sized for 148 SMs on purpose so that
 // the workspace size does not depend on the device queried.
-Split colproj_split(int64_t M, int64_t C, int rp) {
-  const int64_t c_tiles = (C + skinny::cp_cols(rp) - 1) / skinny::cp_cols(rp);
+// `launch_tiles` = column tiles of ALL problems that share the launch (dB and dA go together).
+Split colproj_split(int64_t M, int64_t launch_tiles) {
   const int64_t m_tiles = (M + skinny::CP_BM - 1) / skinny::CP_BM;
   // two CTAs fit per SM: aim for at most one full wave (2*148 CTAs) so that no straggler wave forms
-  int64_t want = (2 * 148) / c_tiles;
+  int64_t want = (2 * 148) / launch_tiles;
   if (want < 1) want = 1;
   if (want > m_tiles) want = m_tiles;
   const int64_t tiles_per = (m_tiles + want - 1) / want;
@@ -142,6 +142,7 @@ Split colproj_split(int64_t M, int64_t C, int rp) {
   s.splits = static_cast<int>((M + s.rows_per_split - 1) / s.rows_per_split);
   return s;
 }
+int64_t colproj_tiles(int64_t C, int rp) { return (C + skinny::cp_cols(rp) - 1) / skinny::cp_cols(rp); }
 
 constexpr int kMaxColTiles = 4096;  // arrival counters per column projection (C <= 4096*64 columns)
 struct Workspace {
@@ -157,8 +158,8 @@ Workspace carve(int64_t M, int64_t K, int64_t N, int r) {
   w.sb16t = off; off += align256(static_cast<size_t>(rp) * N * 2);
   w.dh = off;    off += align256(static_cast<size_t>(M) * rp * 2);
   w.counters = off; off += align256(2 * kMaxColTiles * sizeof(unsigned int));
-  const Split sk = colproj_split(M, K, rp), sn = colproj_split(M, N, rp);
-  const size_t pk = static_cast<size_t>(sk.splits) * K * rp * 4, pn = static_cast<size_t>(sn.splits) * N * rp * 4;
+  const Split sp = colproj_split(M, colproj_tiles(K, rp) + colproj_tiles(N, rp));
+  const size_t pk = static_cast<size_t>(sp.splits) * K * rp * 4, pn = static_cast<size_t>(sp.splits) * N * rp * 4;
   w.partial = off;  off += align256(pn);   // dB partial sums
   w.partial2 = off; off += align256(pk);   // dA partial sums (both column projections share one launch)
   w.total = off;
@@ -267,11 +268,13 @@ int launch_colproj(const ColProjJob* jobs, int njobs, int64_t M, int r, int rp, 
                    cudaStream_t stream) {
   CUtensorMap tmAct[2], tmSmall[2];
   skinny::ColProjParams pp{};
+  int64_t launch_tiles = 0;
+  for (int i = 0; i < njobs; ++i) launch_tiles += colproj_tiles(jobs[i].C, rp);
+  const Split sp = colproj_split(M, launch_tiles);
   for (int i = 0; i < 2; ++i) {
     const ColProjJob& j = jobs[i < njobs ? i : 0];
     if (make_tmap(&tmAct[i], j.act, dtype, j.C, M, j.C, 64, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_128B, "colproj act")) return 1;
     if (make_tmap(&tmSmall[i], j.small, dtype, rp, M, rp, rp, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_NONE, "colproj small")) return 1;
-    const Split sp = colproj_split(M, j.C, rp);
     skinny::ColProjProblem& q = pp.prob[i];
     q.partial = j.partial;
     q.counters = j.counters;
@@ -286,7 +289,7 @@ int launch_colproj(const ColProjJob* jobs, int njobs, int64_t M, int r, int rp, 
     q.C = (int)j.C;
     q.rows_per_split = sp.rows_per_split;
     q.splits = sp.splits;
-    q.c_tiles = static_cast<int>((j.C + skinny::cp_cols(rp) - 1) / skinny::cp_cols(rp));
+    q.c_tiles = static_cast<int>(colproj_tiles(j.C, rp));
     if (q.c_tiles > kMaxColTiles) return fail("column projection over %lld columns exceeds the %d-tile counter table", (long long)j.C, kMaxColTiles);
   }
   const bool bf = dtype == kDtypeBf16;
@@ -559,7 +562,7 @@ int lora_linear_grad_b_static(const void* dY, const void* H, float* dB, int64_t 
   if (check_common(M, /*K=*/8, N, r, dtype)) return 1;
   if (!dY || !H || !dB) return fail("lora_linear_grad_b_static: null pointer argument");
   const int rp = rpad_of(r);
-  const Split sp = colproj_split(M, N, rp);
+  const Split sp = colproj_split(M, colproj_tiles(N, rp));
   const size_t counter_bytes = align256(kMaxColTiles * sizeof(unsigned int));
   const size_t need = counter_bytes + static_cast<size_t>(sp.splits) * static_cast<size_t>(N) * rp * sizeof(float);
   if (need > static_cast<size_t>(LORA_B200_STATIC_SCRATCH_BYTES))

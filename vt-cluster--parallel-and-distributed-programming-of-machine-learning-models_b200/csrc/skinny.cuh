@@ -319,9 +319,9 @@ constexpr int CP_BOX_BYTES = CP_BM * 128;  // 16 KiB: 128 rows x 64 columns
 constexpr int CP_CONSUMERS = 8;
 constexpr int CP_THREADS = (CP_CONSUMERS + 1) * 32;
 // 64-column boxes per tile / ring depth, by padded rank (register and smem budget)
-__host__ __device__ constexpr int cp_boxes(int rpad) { return rpad <= 16 ? 2 : 1; }
+__host__ __device__ constexpr int cp_boxes(int rpad) { return 1; }  // 2 boxes cost the second resident CTA (smem)
 __host__ __device__ constexpr int cp_cols(int rpad) { return 64 * cp_boxes(rpad); }
-__host__ __device__ constexpr int cp_stages(int rpad) { return rpad <= 16 ? 3 : 4; }
+__host__ __device__ constexpr int cp_stages(int rpad) { return 4; }
 template <int kRPad>
 __host__ __device__ constexpr int cp_slot_bytes() {
   return cp_boxes(kRPad) * CP_BOX_BYTES + ((CP_BM * kRPad * 2 + 1023) / 1024) * 1024;
