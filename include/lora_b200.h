@@ -54,7 +54,8 @@ size_t lora_linear_workspace_bytes(int64_t M, int64_t K, int64_t N, int32_t r);
  * finetune_lora_opt_pp.py:109):
  *     H = dropout_p(X) A^T          (written to H, 16-bit, saved for backward)
  *     Y = X W^T + bias + scaling * H B^T
- * p > 0 draws the dropout mask from Philox4x32-10 keyed by (seed, offset) and
+ * p > 0 draws the dropout mask from Philox4x32-10 keyed by (seed, offset) (p is
+ * resolved to 1/16384: an element is dropped with probability round(p*16384)/16384) and
  * writes the keep-bits to keep_mask (needed by backward); p == 0 ignores
  * keep_mask (may be NULL).  Xd (optional, [M,K], may be NULL) receives
  * keep .* X -- the tensor torch autograd would save for lora_A's weight

@@ -4,8 +4,8 @@ Philox4x32-10 (Salmon, Moraes, Dror, Shaw: "Parallel random numbers: as easy as
 1, 2, 3", SC'11), consumed exactly as csrc/common.cuh::dropout_keep_bits does:
 one call per aligned group of 8 consecutive elements of the [M, K] adapter
 input, counter = (g_lo, g_hi, offset_lo, offset_hi), key = (seed_lo, seed_hi),
-element e of the group takes the e-th 16-bit lane and survives iff
-lane >= round(p * 65536).
+element e of the group takes the low 14 bits of the e-th 16-bit lane and
+survives iff lane14 >= round(p * 16384).
 
 The reference draws its mask from torch's CPU generator inside peft's
 nn.Dropout (lora_dropout=0.05 at finetune_lora_distilgpt2.py:101 and
@@ -46,9 +46,9 @@ def philox4x32_10(c0, c1, c2, c3, k0, k1):
     return (c0.astype(np.uint32), c1.astype(np.uint32), c2.astype(np.uint32), c3.astype(np.uint32))
 
 
-def thresh16(p: float) -> int:
-    """Same rounding as the host code in csrc/lora_b200.cu (float32 p * 65536 + 0.5, truncated)."""
-    return int(np.float32(p) * np.float32(65536.0) + np.float32(0.5))
+def thresh14(p: float) -> int:
+    """Same rounding as the host code in csrc/lora_b200.cu (float32 p * 16384 + 0.5, truncated)."""
+    return int(np.float32(p) * np.float32(16384.0) + np.float32(0.5))
 
 
 def keep_bytes(M: int, K: int, p: float, seed: int, offset: int) -> np.ndarray:
@@ -60,10 +60,10 @@ def keep_bytes(M: int, K: int, p: float, seed: int, offset: int) -> np.ndarray:
     o_lo = np.uint32(offset & 0xFFFFFFFF)
     o_hi = np.uint32((offset >> 32) & 0xFFFFFFFF)
     r = philox4x32_10(g_lo, g_hi, o_lo, o_hi, seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
-    t = thresh16(p)
+    t = thresh14(p)
     bits = np.zeros(groups.shape, dtype=np.uint8)
     for e in range(8):
-        lane = (r[e >> 1] >> np.uint32((e & 1) * 16)) & np.uint32(0xFFFF)
+        lane = (r[e >> 1] >> np.uint32((e & 1) * 16)) & np.uint32(0x3FFF)
         bits |= ((lane >= t).astype(np.uint8) << np.uint8(e))
     return bits.reshape(M, K // 8)
 

@@ -221,10 +221,11 @@ __host__ __device__ __forceinline__ uint32_t make_idesc_f16(int fmt, int umma_m,
 }
 
 // ---------------------------------------------------------------------------
-// Philox4x32-10 (Salmon et al., SC'11).  One call yields 128 random bits,
-// consumed as eight 16-bit lanes: one lane per element of an aligned group of
-// eight consecutive elements of the [M,K] dropout input.  The same function is
-// restated in numpy in oracle/philox.py so that CPU and GPU share masks.
+// Philox4x32-10 (Salmon et al., SC'11).  One call yields 128 random bits, consumed as eight
+// 16-bit lanes of which the low 14 bits are used: one lane per element of an aligned group of
+// eight consecutive elements of the [M,K] dropout input; an element survives iff
+// lane14 >= round(p * 16384).  The same function is restated in numpy in oracle/philox.py so
+// that CPU and GPU share masks.
 // ---------------------------------------------------------------------------
 __host__ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
                                                        uint32_t k0, uint32_t k1, uint32_t (&out)[4]) {
@@ -242,9 +243,9 @@ __host__ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1,
   }
   out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
-// keep-bits (bit e set = element e of the group survives) for group `g`.
+// keep-bits (bit e set = element e of the group survives) for group `g`; plain reference form.
 __host__ __device__ __forceinline__ uint32_t dropout_keep_bits(uint64_t g, uint64_t seed, uint64_t offset,
-                                                               uint32_t thresh16) {
+                                                               uint32_t thresh14) {
   uint32_t r[4];
   philox4x32_10(static_cast<uint32_t>(g), static_cast<uint32_t>(g >> 32), static_cast<uint32_t>(offset),
                 static_cast<uint32_t>(offset >> 32), static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32),
@@ -252,8 +253,8 @@ __host__ __device__ __forceinline__ uint32_t dropout_keep_bits(uint64_t g, uint6
   uint32_t bits = 0;
 #pragma unroll
   for (int e = 0; e < 8; ++e) {
-    const uint32_t u = (r[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu;
-    bits |= (u >= thresh16 ? 1u : 0u) << e;
+    const uint32_t u = (r[e >> 1] >> ((e & 1) * 16)) & 0x3FFFu;
+    bits |= (u >= thresh14 ? 1u : 0u) << e;
   }
   return bits;
 }
@@ -275,11 +276,16 @@ __device__ __forceinline__ PhiloxKeys philox_round_keys(uint64_t seed) {
   }
   return rk;
 }
+// thresh14 -> the packed-half constant dropout_keep_masks compares against
+__host__ __device__ __forceinline__ uint32_t dropout_thresh_half2(uint32_t thresh14) {
+  return (thresh14 + 0x0400u) * 0x00010001u;
+}
 // Same draw as dropout_keep_bits, delivered as four AND-masks for the four 32-bit words of a
-// 16-byte chunk of 16-bit elements (0xFFFF per surviving element) plus the packed keep-bits; the
-// per-halfword compares run on the SIMD video path instead of eight scalar compare/select chains.
+// 16-byte chunk of 16-bit elements (0xFFFF per surviving element) plus the packed keep-bits.
+// The 14-bit lanes, offset by 0x0400, are all positive NORMAL fp16 bit patterns (0x0400..0x43FF),
+// whose floating-point order equals their integer order: one HSET2 per word gives both masks.
 __device__ __forceinline__ uint32_t dropout_keep_masks(uint32_t g_lo, uint32_t g_hi, uint32_t off_lo, uint32_t off_hi,
-                                                       const PhiloxKeys& rk, uint32_t thresh2,
+                                                       const PhiloxKeys& rk, uint32_t thresh_h2,
                                                        uint32_t (&mask)[4]) {
   uint32_t c0 = g_lo, c1 = g_hi, c2 = off_lo, c3 = off_hi;
 #pragma unroll
@@ -294,13 +300,17 @@ __device__ __forceinline__ uint32_t dropout_keep_masks(uint32_t g_lo, uint32_t g
     c2 = n2;
   }
   const uint32_t r[4] = {c0, c1, c2, c3};
-  uint32_t bits = 0;
+  const __half2 th = *reinterpret_cast<const __half2*>(&thresh_h2);
 #pragma unroll
   for (int w = 0; w < 4; ++w) {
-    mask[w] = __vcmpgeu2(r[w], thresh2);  // 0xFFFF where the 16-bit lane >= thresh (unsigned)
-    bits |= ((mask[w] & 1u) | ((mask[w] >> 15) & 2u)) << (2 * w);
+    const uint32_t x = (r[w] & 0x3FFF3FFFu) + 0x04000400u;
+    mask[w] = __hge2_mask(*reinterpret_cast<const __half2*>(&x), th);
   }
-  return bits;
+  // byte 0 of each half-word mask -> one bit each: (m0.lo, m0.hi, m1.lo, m1.hi | m2.lo, ...)
+  const uint32_t w01 = __byte_perm(mask[0], mask[1], 0x6420);
+  const uint32_t w23 = __byte_perm(mask[2], mask[3], 0x6420);
+  const uint32_t spread = (w01 & 0x08040201u) | (w23 & 0x80402010u);
+  return (spread * 0x01010101u) >> 24;
 }
 #endif
 

@@ -223,7 +223,7 @@ int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out,
   rp_p.dropout = p > 0.f ? 1 : 0;
   rp_p.seed = seed;
   rp_p.offset = offset;
-  rp_p.thresh16 = static_cast<uint32_t>(p * 65536.0f + 0.5f);
+  rp_p.thresh14 = static_cast<uint32_t>(p * 16384.0f + 0.5f);
   const bool bf = dtype == kDtypeBf16;
 #define RP_CASE(BF, RP) return launch_rowproj_t<BF, RP>(tmAct, tmP, tmXd, rp_p, stream);
   if (bf) {
@@ -429,10 +429,10 @@ int static_scratch_ptr(void** out) {
   return 0;
 }
 
-__global__ void keep_mask_kernel(uint8_t* keep, long long groups, uint64_t seed, uint64_t offset, uint32_t thresh16) {
+__global__ void keep_mask_kernel(uint8_t* keep, long long groups, uint64_t seed, uint64_t offset, uint32_t thresh14) {
   for (long long g = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; g < groups;
        g += static_cast<long long>(gridDim.x) * blockDim.x)
-    keep[g] = static_cast<uint8_t>(lb::dropout_keep_bits(static_cast<uint64_t>(g), seed, offset, thresh16));
+    keep[g] = static_cast<uint8_t>(lb::dropout_keep_bits(static_cast<uint64_t>(g), seed, offset, thresh14));
 }
 
 }  // namespace
@@ -592,7 +592,7 @@ int lora_dropout_keep_mask(uint8_t* keep_mask, int64_t M, int64_t K, float p, ui
   if (!(p >= 0.f && p < 1.f)) return fail("dropout p must be in [0,1); got %f", (double)p);
   const long long groups = static_cast<long long>(M) * (K / 8);
   const int grid = static_cast<int>(std::min<long long>((groups + 255) / 256, 4096));
-  keep_mask_kernel<<<grid, 256, 0, stream>>>(keep_mask, groups, seed, offset, static_cast<uint32_t>(p * 65536.0f + 0.5f));
+  keep_mask_kernel<<<grid, 256, 0, stream>>>(keep_mask, groups, seed, offset, static_cast<uint32_t>(p * 16384.0f + 0.5f));
   CUDA_TRY(cudaGetLastError());
   return 0;
 }

@@ -114,7 +114,7 @@ __global__ void pack_adapters_kernel(const float* __restrict__ A, const float* _
 // ---------------------------------------------------------------------------
 constexpr int RP_BM = 64;
 constexpr int RP_BK = 64;
-constexpr int RP_STAGES = 5;
+constexpr int RP_STAGES = 6;
 constexpr int RP_ACT_BYTES = RP_BM * 128;  // 8 KiB
 constexpr int RP_CONSUMERS = 8;
 constexpr int RP_THREADS = (RP_CONSUMERS + 1) * 32;
@@ -135,11 +135,11 @@ struct RowProjParams {
   int dropout;  // 0/1
   int store_xd;  // 1: TMA-store the masked tiles (keep .* Act, unscaled) through tmXd
   uint64_t seed, offset;
-  uint32_t thresh16;
+  uint32_t thresh14;  // round(p * 16384)
 };
 
 template <bool kBf16, int kRPad>
-__global__ void __launch_bounds__(RP_THREADS, (kRPad <= 16 ? 3 : 2))
+__global__ void __launch_bounds__(RP_THREADS)
     rowproj_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constant__ CUtensorMap tmP,
                    const __grid_constant__ CUtensorMap tmXd, const RowProjParams p) {
   constexpr int SLOT = rp_slot_bytes<kRPad>();
@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(RP_THREADS, (kRPad <= 16 ? 3 : 2))
   PhiloxKeys rk;
   uint64_t gbase[2] = {0, 0};
   bool row_ok[2] = {false, false};
-  const uint32_t thresh2 = p.thresh16 | (p.thresh16 << 16);
+  const uint32_t thresh2 = dropout_thresh_half2(p.thresh14);
   const uint32_t off_lo = static_cast<uint32_t>(p.offset), off_hi = static_cast<uint32_t>(p.offset >> 32);
   if (p.dropout) {
     rk = philox_round_keys(p.seed);
