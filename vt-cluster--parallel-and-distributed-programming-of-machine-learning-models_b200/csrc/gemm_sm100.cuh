@@ -60,6 +60,7 @@ struct Params {
   const void* dh;  // [M, dh_ld] dtype, dh_ld = padded rank (16/32/64), padding columns zero
   int dh_ld;
   const void* a16;      // A^T as [N, dh_ld] dtype (rank index contiguous), padding columns zero
+  const void* a16_rows; // A as [dh_ld, N] dtype (column index contiguous), padding rows zero
   const uint8_t* keep;  // [M, N/8] keep bits
   float inv_keep;
 };
@@ -281,6 +282,12 @@ __global__ void __launch_bounds__(THREADS, 1)
     const int dtype = p.dtype;
     const int keep_ld = p.N >> 3;
     const int mk_steps = kMasked ? p.dh_ld / 16 : 0;  // k16 steps of the rank-r product (1, 2 or 4)
+    // Masked mode, padded rank 16 (every adapter of the reference): dH.A is formed on the CUDA cores
+    // from an fp32 copy of the tile's 16 x 256 slice of A that the four epilogue warps stage in
+    // their scratch buffers while the main loop runs.  (Warp-level MMAs would queue behind the UMMA
+    // stream on the one tensor pipe, and re-fetching A fragments per chunk exposes L2 latency.)
+    // Wider ranks keep the warp-MMA path below.
+    const bool use_fma = kMasked && p.dh_ld == 16;
     for (int tile = tile0; tile < num_tiles; tile += tile_step, ++it) {
       int m_blk, n_blk;
       tile_coords(tile, num_m, num_n, m_blk, n_blk);
@@ -293,7 +300,46 @@ __global__ void __launch_bounds__(THREADS, 1)
       // dH rows of this warp as mma.sync A-fragments (2 m16 blocks x up to 4 k16 steps),
       // fetched while the main loop of this tile is still running.
       uint32_t dh_frag[2][4][4];
+      float dhv[16];
       if constexpr (kMasked) {
+        if (use_fma) {
+          asm volatile("bar.sync 2, 128;" ::: "memory");  // every warp is done with the previous tile's A slice
+          const int t128 = ew * 32 + lane;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int g = t128 + 128 * i;        // 512 groups of 8 columns: j = g / 32, column group g % 32
+            const int j = g >> 5, cg = g & 31;
+            const int col = n_blk * BN + cg * 8;
+            uint4 raw = make_uint4(0u, 0u, 0u, 0u);
+            if (col < p.N)
+              raw = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.a16_rows) +
+                                                        static_cast<size_t>(j) * p.N + col));
+            const float2 f0 = unpack2(raw.x, dtype), f1 = unpack2(raw.y, dtype), f2 = unpack2(raw.z, dtype),
+                         f3 = unpack2(raw.w, dtype);
+            // region (cg / 8) = scratch buffer of epilogue warp cg/8: [16 j][64 cols] fp32
+            float* dstA = reinterpret_cast<float*>(epi_base + (cg >> 3) * 2 * EPI_BUF_BYTES + EPI_BUF_BYTES) + j * 64 +
+                          (cg & 7) * 8;
+            *reinterpret_cast<float4*>(dstA) = make_float4(f0.x, f0.y, f1.x, f1.y);
+            *reinterpret_cast<float4*>(dstA + 4) = make_float4(f2.x, f2.y, f3.x, f3.y);
+          }
+          asm volatile("bar.sync 2, 128;" ::: "memory");  // slice complete
+#pragma unroll
+          for (int j = 0; j < 16; ++j) dhv[j] = 0.f;
+          if (row_ok) {
+            const uint4* dhp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.dh) +
+                                                              static_cast<size_t>(row) * 16);
+            const uint4 d0 = __ldg(dhp), d1 = __ldg(dhp + 1);
+            const uint32_t w8[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float2 f = unpack2(w8[e], dtype);
+              dhv[2 * e] = f.x * p.inv_keep;
+              dhv[2 * e + 1] = f.y * p.inv_keep;
+            }
+          }
+        }
+      }
+      if constexpr (kMasked) if (!use_fma) {
         const uint32_t* dh32 = reinterpret_cast<const uint32_t*>(p.dh);
 #pragma unroll
         for (int mb = 0; mb < 2; ++mb)
@@ -343,7 +389,7 @@ __global__ void __launch_bounds__(THREADS, 1)
               }
             }
           }
-          if constexpr (kMasked) {
+          if constexpr (kMasked) if (!use_fma) {
             // T[32 rows, 32 cols] = dH[32, rp] * A[rp, c..c+31] on the warp's tensor-core path,
             // overlapping the TMEM load above.  B-fragments come from a16t [N, rp] (j contiguous).
             float t[2][4][4];
@@ -407,7 +453,30 @@ __global__ void __launch_bounds__(THREADS, 1)
               }
             }
           }
-          if constexpr (kMasked) {
+          if constexpr (kMasked) if (use_fma) {
+            // low[i] = sum_j dH'[row, j] * A[j, c + i]: A rows are warp-uniform smem reads (broadcast)
+            const float* At = reinterpret_cast<const float*>(epi_base + cb * 2 * EPI_BUF_BYTES + EPI_BUF_BYTES) + h * 32;
+            float low[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) low[i] = 0.f;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              if (j < p.masked_r) {
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                  const float4 a4 = *reinterpret_cast<const float4*>(At + j * 64 + q * 4);
+                  low[q * 4 + 0] = fmaf(dhv[j], a4.x, low[q * 4 + 0]);
+                  low[q * 4 + 1] = fmaf(dhv[j], a4.y, low[q * 4 + 1]);
+                  low[q * 4 + 2] = fmaf(dhv[j], a4.z, low[q * 4 + 2]);
+                  low[q * 4 + 3] = fmaf(dhv[j], a4.w, low[q * 4 + 3]);
+                }
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if ((kbits >> i) & 1u) v[i] = __float_as_uint(__uint_as_float(v[i]) + low[i]);
+          }
+          if constexpr (kMasked) if (!use_fma) {
 #pragma unroll
             for (int f = 0; f < 8; ++f) {
               const float4 t4 = *reinterpret_cast<const float4*>(scratch + lane * 32 + ((f ^ (lane & 7)) << 2));
