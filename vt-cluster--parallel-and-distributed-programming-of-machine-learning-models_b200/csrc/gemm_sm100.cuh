@@ -32,9 +32,12 @@ constexpr int A_TILE_BYTES = BM * BK * 2;  // 16 KiB: the CTA's own 128 rows of 
 // kPair = true : a 2-CTA cluster per 256x256 tile (tcgen05 cta_group::2, UMMA M = 256); each
 //                CTA stages its own 128 rows of A1 and HALF of the B tile (128 rows, 16 KiB),
 //                so L2 -> SMEM traffic per flop halves and 6 stages of 32 KiB fit.
-template <bool kPair>
+// kMasked trades one ring stage for a 32 KiB scratch region (the epilogue's staged A slice or
+// the warp-MMA transposition buffers), so that output staging stays double-buffered.
+constexpr int MASK_SCRATCH_BYTES = 32 * 1024;
+template <bool kPair, bool kMasked = false>
 struct Cfg {
-  static constexpr int STAGES = kPair ? 6 : 4;
+  static constexpr int STAGES = (kPair ? 6 : 4) - (kMasked ? 1 : 0);
   static constexpr int B_ROWS = kPair ? BN / 2 : BN;  // rows of the B tile held by one CTA
   static constexpr int B_TILE_BYTES = B_ROWS * BK * 2;
   static constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
@@ -105,7 +108,7 @@ __global__ void __launch_bounds__(THREADS, 1)
     gemm_lora_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                      const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
                      const __grid_constant__ CUtensorMap tmD, const Params p) {
-  using C = Cfg<kPair>;
+  using C = Cfg<kPair, kMasked>;
   constexpr int STAGES = C::STAGES;
   constexpr int STAGE_BYTES = C::STAGE_BYTES;
   constexpr int B_ROWS = C::B_ROWS;
@@ -113,7 +116,8 @@ __global__ void __launch_bounds__(THREADS, 1)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* stage_base = smem;
   uint8_t* epi_base = smem + STAGES * STAGE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_base + EPI_BYTES);
+  uint8_t* mask_scratch = epi_base + EPI_BYTES;  // kMasked only
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_base + EPI_BYTES + (kMasked ? MASK_SCRATCH_BYTES : 0));
   uint64_t* full = bars;
   uint64_t* empty = bars + STAGES;
   uint64_t* tmem_full = bars + 2 * STAGES;
@@ -274,9 +278,9 @@ __global__ void __launch_bounds__(THREADS, 1)
     // ===================== epilogue =====================
     const int ew = warp - 4;  // == warp % 4: the TMEM lane quadrant this warp may touch
     uint8_t* my_stage = epi_base + ew * 2 * EPI_BUF_BYTES;
-    // Masked mode stages through buffer 0 only; buffer 1 is the 32x32 fp32 scratch through
-    // which the warp-level MMA result is transposed to one-row-per-thread.
-    float* scratch = reinterpret_cast<float*>(my_stage + EPI_BUF_BYTES);
+    // Masked mode, wide ranks: a 32x32 fp32 scratch per warp through which the warp-level MMA
+    // result is transposed to one-row-per-thread.
+    float* scratch = reinterpret_cast<float*>(mask_scratch + ew * EPI_BUF_BYTES);
     uint32_t sbuf = 0;
     uint32_t it = 0;
     const int dtype = p.dtype;
@@ -316,9 +320,8 @@ __global__ void __launch_bounds__(THREADS, 1)
                                                         static_cast<size_t>(j) * p.N + col));
             const float2 f0 = unpack2(raw.x, dtype), f1 = unpack2(raw.y, dtype), f2 = unpack2(raw.z, dtype),
                          f3 = unpack2(raw.w, dtype);
-            // region (cg / 8) = scratch buffer of epilogue warp cg/8: [16 j][64 cols] fp32
-            float* dstA = reinterpret_cast<float*>(epi_base + (cg >> 3) * 2 * EPI_BUF_BYTES + EPI_BUF_BYTES) + j * 64 +
-                          (cg & 7) * 8;
+            // region (cg / 8) of the scratch: [16 j][64 cols] fp32 for the tile's 64-column block cg/8
+            float* dstA = reinterpret_cast<float*>(mask_scratch + (cg >> 3) * EPI_BUF_BYTES) + j * 64 + (cg & 7) * 8;
             *reinterpret_cast<float4*>(dstA) = make_float4(f0.x, f0.y, f1.x, f1.y);
             *reinterpret_cast<float4*>(dstA + 4) = make_float4(f2.x, f2.y, f3.x, f3.y);
           }
@@ -365,11 +368,9 @@ __global__ void __launch_bounds__(THREADS, 1)
         const int col0 = n_blk * BN + cb * 64;
         if (col0 >= p.N) break;  // warp-uniform
         // the staging buffer we are about to overwrite must have been read by its TMA store
-        if (lane == 0) {
-          if constexpr (kMasked) bulk_wait_group_read<0>(); else bulk_wait_group_read<1>();
-        }
+        if (lane == 0) bulk_wait_group_read<1>();
         __syncwarp();
-        uint8_t* sdst = my_stage + (kMasked ? 0u : sbuf) * EPI_BUF_BYTES + lane * 128;
+        uint8_t* sdst = my_stage + sbuf * EPI_BUF_BYTES + lane * 128;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           uint32_t v[32];
@@ -455,7 +456,7 @@ __global__ void __launch_bounds__(THREADS, 1)
           }
           if constexpr (kMasked) if (use_fma) {
             // low[i] = sum_j dH'[row, j] * A[j, c + i]: A rows are warp-uniform smem reads (broadcast)
-            const float* At = reinterpret_cast<const float*>(epi_base + cb * 2 * EPI_BUF_BYTES + EPI_BUF_BYTES) + h * 32;
+            const float* At = reinterpret_cast<const float*>(mask_scratch + cb * EPI_BUF_BYTES) + h * 32;
             float low[32];
 #pragma unroll
             for (int i = 0; i < 32; ++i) low[i] = 0.f;
@@ -502,7 +503,7 @@ __global__ void __launch_bounds__(THREADS, 1)
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
-          tma_store_2d(&tmD, my_stage + (kMasked ? 0u : sbuf) * EPI_BUF_BYTES, col0, rbase);
+          tma_store_2d(&tmD, my_stage + sbuf * EPI_BUF_BYTES, col0, rbase);
           bulk_commit_group();
         }
         sbuf ^= 1u;
