@@ -63,7 +63,6 @@ struct Params {
   const void* dh;  // [M, dh_ld] dtype, dh_ld = padded rank (16/32/64), padding columns zero
   int dh_ld;
   const void* a16;      // A^T as [N, dh_ld] dtype (rank index contiguous), padding columns zero
-  const void* a16_rows; // A as [dh_ld, N] dtype (column index contiguous), padding rows zero
   const uint8_t* keep;  // [M, N/8] keep bits
   float inv_keep;
 };
@@ -286,12 +285,12 @@ __global__ void __launch_bounds__(THREADS, 1)
     const int dtype = p.dtype;
     const int keep_ld = p.N >> 3;
     const int mk_steps = kMasked ? p.dh_ld / 16 : 0;  // k16 steps of the rank-r product (1, 2 or 4)
-    // Masked mode, padded rank 16 (every adapter of the reference): dH.A is formed on the CUDA cores
-    // from an fp32 copy of the tile's 16 x 256 slice of A that the four epilogue warps stage in
-    // their scratch buffers while the main loop runs.  (Warp-level MMAs would queue behind the UMMA
-    // stream on the one tensor pipe, and re-fetching A fragments per chunk exposes L2 latency.)
-    // Wider ranks keep the warp-MMA path below.
-    const bool use_fma = kMasked && p.dh_ld == 16;
+    // Masked mode: dH.A for a 32x32 chunk is a handful of warp-level MMAs.  Their B-fragments
+    // (A^T, rank index contiguous) come from the tile's 256-column slice of a16t, which the four
+    // epilogue warps copy into smem once per tile while the main loop runs (one contiguous block of
+    // 256*rp*2 bytes); only the widest rank (rp = 64, slice too big) reads them from L2 per chunk.
+    const bool slice_in_smem = kMasked && p.dh_ld <= 32;
+    const uint32_t* aslice = reinterpret_cast<const uint32_t*>(mask_scratch + 4 * EPI_BUF_BYTES);  // [256][rp] 16-bit
     for (int tile = tile0; tile < num_tiles; tile += tile_step, ++it) {
       int m_blk, n_blk;
       tile_coords(tile, num_m, num_n, m_blk, n_blk);
@@ -304,45 +303,20 @@ __global__ void __launch_bounds__(THREADS, 1)
       // dH rows of this warp as mma.sync A-fragments (2 m16 blocks x up to 4 k16 steps),
       // fetched while the main loop of this tile is still running.
       uint32_t dh_frag[2][4][4];
-      float dhv[16];
       if constexpr (kMasked) {
-        if (use_fma) {
-          asm volatile("bar.sync 2, 128;" ::: "memory");  // every warp is done with the previous tile's A slice
-          const int t128 = ew * 32 + lane;
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int g = t128 + 128 * i;        // 512 groups of 8 columns: j = g / 32, column group g % 32
-            const int j = g >> 5, cg = g & 31;
-            const int col = n_blk * BN + cg * 8;
-            uint4 raw = make_uint4(0u, 0u, 0u, 0u);
-            if (col < p.N)
-              raw = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.a16_rows) +
-                                                        static_cast<size_t>(j) * p.N + col));
-            const float2 f0 = unpack2(raw.x, dtype), f1 = unpack2(raw.y, dtype), f2 = unpack2(raw.z, dtype),
-                         f3 = unpack2(raw.w, dtype);
-            // region (cg / 8) of the scratch: [16 j][64 cols] fp32 for the tile's 64-column block cg/8
-            float* dstA = reinterpret_cast<float*>(mask_scratch + (cg >> 3) * EPI_BUF_BYTES) + j * 64 + (cg & 7) * 8;
-            *reinterpret_cast<float4*>(dstA) = make_float4(f0.x, f0.y, f1.x, f1.y);
-            *reinterpret_cast<float4*>(dstA + 4) = make_float4(f2.x, f2.y, f3.x, f3.y);
-          }
+        if (slice_in_smem) {
+          asm volatile("bar.sync 2, 128;" ::: "memory");  // every warp is done with the previous tile's slice
+          const int ncol = min(BN, p.N - n_blk * BN);
+          const int n16 = ncol * p.dh_ld / 8;  // 16-byte units to copy (contiguous in a16t)
+          const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.a16) +
+                                                            static_cast<size_t>(n_blk) * BN * p.dh_ld);
+          uint4* dst = reinterpret_cast<uint4*>(mask_scratch + 4 * EPI_BUF_BYTES);
+          for (int i = ew * 32 + lane; i < BN * p.dh_ld / 8; i += 128)
+            dst[i] = i < n16 ? __ldg(src + i) : make_uint4(0u, 0u, 0u, 0u);
           asm volatile("bar.sync 2, 128;" ::: "memory");  // slice complete
-#pragma unroll
-          for (int j = 0; j < 16; ++j) dhv[j] = 0.f;
-          if (row_ok) {
-            const uint4* dhp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.dh) +
-                                                              static_cast<size_t>(row) * 16);
-            const uint4 d0 = __ldg(dhp), d1 = __ldg(dhp + 1);
-            const uint32_t w8[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const float2 f = unpack2(w8[e], dtype);
-              dhv[2 * e] = f.x * p.inv_keep;
-              dhv[2 * e + 1] = f.y * p.inv_keep;
-            }
-          }
         }
       }
-      if constexpr (kMasked) if (!use_fma) {
+      if constexpr (kMasked) {
         const uint32_t* dh32 = reinterpret_cast<const uint32_t*>(p.dh);
 #pragma unroll
         for (int mb = 0; mb < 2; ++mb)
@@ -390,7 +364,7 @@ __global__ void __launch_bounds__(THREADS, 1)
               }
             }
           }
-          if constexpr (kMasked) if (!use_fma) {
+          if constexpr (kMasked) {
             // T[32 rows, 32 cols] = dH[32, rp] * A[rp, c..c+31] on the warp's tensor-core path,
             // overlapping the TMEM load above.  B-fragments come from a16t [N, rp] (j contiguous).
             float t[2][4][4];
@@ -408,9 +382,15 @@ __global__ void __launch_bounds__(THREADS, 1)
 #pragma unroll
                 for (int nb = 0; nb < 4; ++nb) {
                   const int col = c + nb * 8 + (lane >> 2);
-                  const size_t o = (static_cast<size_t>(col) * p.dh_ld + ks * 16 + (lane & 3) * 2) >> 1;
-                  bfr[nb][0] = col < p.N ? __ldg(at32 + o) : 0u;
-                  bfr[nb][1] = col < p.N ? __ldg(at32 + o + 4) : 0u;
+                  if (slice_in_smem) {
+                    const int o = ((col - n_blk * BN) * p.dh_ld + ks * 16 + (lane & 3) * 2) >> 1;
+                    bfr[nb][0] = aslice[o];
+                    bfr[nb][1] = aslice[o + 4];
+                  } else {
+                    const size_t o = (static_cast<size_t>(col) * p.dh_ld + ks * 16 + (lane & 3) * 2) >> 1;
+                    bfr[nb][0] = col < p.N ? __ldg(at32 + o) : 0u;
+                    bfr[nb][1] = col < p.N ? __ldg(at32 + o + 4) : 0u;
+                  }
                 }
 #pragma unroll
                 for (int mb = 0; mb < 2; ++mb)
@@ -454,30 +434,7 @@ __global__ void __launch_bounds__(THREADS, 1)
               }
             }
           }
-          if constexpr (kMasked) if (use_fma) {
-            // low[i] = sum_j dH'[row, j] * A[j, c + i]: A rows are warp-uniform smem reads (broadcast)
-            const float* At = reinterpret_cast<const float*>(mask_scratch + cb * EPI_BUF_BYTES) + h * 32;
-            float low[32];
-#pragma unroll
-            for (int i = 0; i < 32; ++i) low[i] = 0.f;
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              if (j < p.masked_r) {
-#pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                  const float4 a4 = *reinterpret_cast<const float4*>(At + j * 64 + q * 4);
-                  low[q * 4 + 0] = fmaf(dhv[j], a4.x, low[q * 4 + 0]);
-                  low[q * 4 + 1] = fmaf(dhv[j], a4.y, low[q * 4 + 1]);
-                  low[q * 4 + 2] = fmaf(dhv[j], a4.z, low[q * 4 + 2]);
-                  low[q * 4 + 3] = fmaf(dhv[j], a4.w, low[q * 4 + 3]);
-                }
-              }
-            }
-#pragma unroll
-            for (int i = 0; i < 32; ++i)
-              if ((kbits >> i) & 1u) v[i] = __float_as_uint(__uint_as_float(v[i]) + low[i]);
-          }
-          if constexpr (kMasked) if (!use_fma) {
+          if constexpr (kMasked) {
 #pragma unroll
             for (int f = 0; f < 8; ++f) {
               const float4 t4 = *reinterpret_cast<const float4*>(scratch + lane * 32 + ((f ^ (lane & 7)) << 2));
