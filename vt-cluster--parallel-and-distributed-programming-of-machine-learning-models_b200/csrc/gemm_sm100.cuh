@@ -63,6 +63,7 @@ struct Params {
   const void* dh;  // [M, dh_ld] dtype, dh_ld = padded rank (16/32/64), padding columns zero
   int dh_ld;
   const void* a16;      // A^T as [N, dh_ld] dtype (rank index contiguous), padding columns zero
+  const void* a16_rows; // A as [dh_ld, N] dtype (column index contiguous), padding rows zero
   const uint8_t* keep;  // [M, N/8] keep bits
   float inv_keep;
 };
@@ -289,7 +290,14 @@ __global__ void __launch_bounds__(THREADS, 1)
     // (A^T, rank index contiguous) come from the tile's 256-column slice of a16t, which the four
     // epilogue warps copy into smem once per tile while the main loop runs (one contiguous block of
     // 256*rp*2 bytes); only the widest rank (rp = 64, slice too big) reads them from L2 per chunk.
-    const bool slice_in_smem = kMasked && p.dh_ld <= 32;
+    const bool slice_in_smem = kMasked && p.dh_ld == 32;
+    // Padded rank 16 (every adapter of the reference): the warp-level MMAs would queue behind the
+    // UMMA stream on the one tensor pipe, so dH.A is formed on the CUDA cores instead, in a compact
+    // runtime loop over the rank: A's 16 x 256 slice as fp32 in smem (row reads are warp-uniform
+    // broadcasts), this thread's dH row in a per-warp smem column (scratch + 16 KiB).
+    const bool use_fma = kMasked && p.dh_ld == 16;
+    const float* fslice = reinterpret_cast<const float*>(mask_scratch);                      // [16 j][256 cols]
+    float* dh_col = reinterpret_cast<float*>(mask_scratch + 4 * EPI_BUF_BYTES) + ew * 16 * 32;  // [16 j][32 lanes]
     const uint32_t* aslice = reinterpret_cast<const uint32_t*>(mask_scratch + 4 * EPI_BUF_BYTES);  // [256][rp] 16-bit
     for (int tile = tile0; tile < num_tiles; tile += tile_step, ++it) {
       int m_blk, n_blk;
@@ -304,6 +312,40 @@ __global__ void __launch_bounds__(THREADS, 1)
       // fetched while the main loop of this tile is still running.
       uint32_t dh_frag[2][4][4];
       if constexpr (kMasked) {
+        if (use_fma) {
+          asm volatile("bar.sync 2, 128;" ::: "memory");  // every warp is done with the previous tile's slice
+          const int t128 = ew * 32 + lane;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int g = t128 + 128 * i;  // 512 groups of 8 columns: j = g / 32, column group g % 32
+            const int j = g >> 5, cg = g & 31;
+            const int col = n_blk * BN + cg * 8;
+            uint4 raw = make_uint4(0u, 0u, 0u, 0u);
+            if (col < p.N)
+              raw = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.a16_rows) +
+                                                        static_cast<size_t>(j) * p.N + col));
+            const float2 f0 = unpack2(raw.x, dtype), f1 = unpack2(raw.y, dtype), f2 = unpack2(raw.z, dtype),
+                         f3 = unpack2(raw.w, dtype);
+            float* dstA = reinterpret_cast<float*>(mask_scratch) + j * BN + cg * 8;
+            *reinterpret_cast<float4*>(dstA) = make_float4(f0.x, f0.y, f1.x, f1.y);
+            *reinterpret_cast<float4*>(dstA + 4) = make_float4(f2.x, f2.y, f3.x, f3.y);
+          }
+          uint4 d0 = make_uint4(0u, 0u, 0u, 0u), d1 = d0;
+          if (row_ok) {
+            const uint4* dhp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.dh) +
+                                                              static_cast<size_t>(row) * 16);
+            d0 = __ldg(dhp);
+            d1 = __ldg(dhp + 1);
+          }
+          const uint32_t w8[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float2 f = unpack2(w8[e], dtype);
+            dh_col[(2 * e) * 32 + lane] = f.x * p.inv_keep;
+            dh_col[(2 * e + 1) * 32 + lane] = f.y * p.inv_keep;
+          }
+          asm volatile("bar.sync 2, 128;" ::: "memory");  // slice (and every warp's dH column) complete
+        }
         if (slice_in_smem) {
           asm volatile("bar.sync 2, 128;" ::: "memory");  // every warp is done with the previous tile's slice
           const int ncol = min(BN, p.N - n_blk * BN);
@@ -316,7 +358,7 @@ __global__ void __launch_bounds__(THREADS, 1)
           asm volatile("bar.sync 2, 128;" ::: "memory");  // slice complete
         }
       }
-      if constexpr (kMasked) {
+      if constexpr (kMasked) if (!use_fma) {
         const uint32_t* dh32 = reinterpret_cast<const uint32_t*>(p.dh);
 #pragma unroll
         for (int mb = 0; mb < 2; ++mb)
@@ -364,7 +406,7 @@ __global__ void __launch_bounds__(THREADS, 1)
               }
             }
           }
-          if constexpr (kMasked) {
+          if constexpr (kMasked) if (!use_fma) {
             // T[32 rows, 32 cols] = dH[32, rp] * A[rp, c..c+31] on the warp's tensor-core path,
             // overlapping the TMEM load above.  B-fragments come from a16t [N, rp] (j contiguous).
             float t[2][4][4];
@@ -434,7 +476,30 @@ __global__ void __launch_bounds__(THREADS, 1)
               }
             }
           }
-          if constexpr (kMasked) {
+          if constexpr (kMasked) if (use_fma) {
+            // low[i] = sum_j dH'[row, j] * A[j, c + i]
+            float low[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) low[i] = 0.f;
+            const float* Ac = fslice + cb * 64 + h * 32;
+#pragma unroll 2
+            for (int j = 0; j < p.masked_r; ++j) {
+              const float d = dh_col[j * 32 + lane];
+              const float4* Ar = reinterpret_cast<const float4*>(Ac + j * BN);
+#pragma unroll
+              for (int q = 0; q < 8; ++q) {
+                const float4 a4 = Ar[q];
+                low[q * 4 + 0] = fmaf(d, a4.x, low[q * 4 + 0]);
+                low[q * 4 + 1] = fmaf(d, a4.y, low[q * 4 + 1]);
+                low[q * 4 + 2] = fmaf(d, a4.z, low[q * 4 + 2]);
+                low[q * 4 + 3] = fmaf(d, a4.w, low[q * 4 + 3]);
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if ((kbits >> i) & 1u) v[i] = __float_as_uint(__uint_as_float(v[i]) + low[i]);
+          }
+          if constexpr (kMasked) if (!use_fma) {
 #pragma unroll
             for (int f = 0; f < 8; ++f) {
               const float4 t4 = *reinterpret_cast<const float4*>(scratch + lane * 32 + ((f ^ (lane & 7)) << 2));

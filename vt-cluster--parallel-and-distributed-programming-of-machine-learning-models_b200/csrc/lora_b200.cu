@@ -314,6 +314,7 @@ struct GemmArgs {
   int masked_r;
   const void* dh;
   const void* a16;
+  const void* a16_rows;
   const uint8_t* keep;
   float inv_keep;
 };
@@ -379,6 +380,7 @@ int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, 
   p.dh = g.dh;
   p.dh_ld = g.rp > 0 ? g.rp : rpad_of(g.masked_r > 0 ? g.masked_r : 1);
   p.a16 = g.a16;
+  p.a16_rows = g.a16_rows;
   p.keep = g.keep;
   p.inv_keep = g.inv_keep;
 
@@ -519,7 +521,8 @@ int lora_linear_bwd(const void* dY, const void* X, const void* W, const float* A
       g.rp = 0;
       g.masked_r = r;
       g.dh = dH;
-      g.a16 = ws + w.a16t;  // [K, rp]: rank index contiguous, as the epilogue's B-fragments want
+      g.a16 = ws + w.a16t;      // [K, rp]: rank index contiguous, as the warp-MMA B-fragments want
+      g.a16_rows = ws + w.a16;  // [rp, K]: column index contiguous, for the staged fp32 slice (rp == 16)
       g.keep = keep;
     } else {
       g.A2 = dH;
