@@ -175,26 +175,20 @@ int check_common(int64_t M, int64_t K, int64_t N, int r, int dtype) {
   return 0;
 }
 
-// Adapter packing (+ counter reset); with keep_out != null also the dropout draw for an [M, K] input.
 int launch_pack(const float* A, const float* B, uint8_t* ws, const Workspace& w, int64_t K, int64_t N, int r, float s,
-                int dtype, uint8_t* keep_out, int64_t M, float p, uint64_t seed, uint64_t offset, int sm_count,
-                cudaStream_t stream) {
+                int dtype, cudaStream_t stream) {
   const int rp = rpad_of(r);
   const long long total = static_cast<long long>(rp) * (K + N);
-  const long long groups = keep_out ? static_cast<long long>(M) * (K / 8) : 0;
-  long long blocks = (std::max(total, groups) + 255) / 256;
-  const int grid = static_cast<int>(std::min<long long>(blocks, static_cast<long long>(sm_count) * 8));
-  const uint32_t th = static_cast<uint32_t>(p * 16384.0f + 0.5f);
-  unsigned int* counters = (unsigned int*)(ws + w.counters);
+  const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, 2048));
   if (dtype == kDtypeBf16)
     skinny::pack_adapters_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(
         A, B, (__nv_bfloat16*)(ws + w.a16), (__nv_bfloat16*)(ws + w.a16t), (__nv_bfloat16*)(ws + w.sb16),
-        (__nv_bfloat16*)(ws + w.sb16t), (int)K, (int)N, r, rp, s, counters, 2 * kMaxColTiles, keep_out, groups, seed,
-        offset, th);
+        (__nv_bfloat16*)(ws + w.sb16t), (int)K, (int)N, r, rp, s, (unsigned int*)(ws + w.counters), 2 * kMaxColTiles);
   else
-    skinny::pack_adapters_kernel<__half><<<grid, 256, 0, stream>>>(
-        A, B, (__half*)(ws + w.a16), (__half*)(ws + w.a16t), (__half*)(ws + w.sb16), (__half*)(ws + w.sb16t), (int)K,
-        (int)N, r, rp, s, counters, 2 * kMaxColTiles, keep_out, groups, seed, offset, th);
+    skinny::pack_adapters_kernel<__half><<<grid, 256, 0, stream>>>(A, B, (__half*)(ws + w.a16), (__half*)(ws + w.a16t),
+                                                                    (__half*)(ws + w.sb16), (__half*)(ws + w.sb16t),
+                                                                    (int)K, (int)N, r, rp, s,
+                                                                    (unsigned int*)(ws + w.counters), 2 * kMaxColTiles);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -209,8 +203,8 @@ int launch_rowproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmP, const CUt
 }
 
 // out[M, rp] = out_scale * (keep .* act)[M, C] * P[rp, C]^T
-int launch_rowproj(const void* act, const void* P, void* out, const uint8_t* keep, void* xd_out, int64_t M, int64_t C,
-                   int rp, int dtype, float out_scale, cudaStream_t stream) {
+int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out, void* xd_out, int64_t M, int64_t C,
+                   int rp, int dtype, float out_scale, float p, uint64_t seed, uint64_t offset, cudaStream_t stream) {
   CUtensorMap tmAct, tmP, tmXd;
   if (make_tmap(&tmAct, act, dtype, C, M, C, skinny::RP_BK, skinny::RP_BM, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj act")) return 1;
   if (make_tmap(&tmP, P, dtype, C, rp, C, skinny::RP_BK, rp, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj P")) return 1;
@@ -220,13 +214,16 @@ int launch_rowproj(const void* act, const void* P, void* out, const uint8_t* kee
     tmXd = tmAct;
   }
   skinny::RowProjParams rp_p;
-  rp_p.store_xd = (xd_out != nullptr && keep != nullptr) ? 1 : 0;
+  rp_p.store_xd = (xd_out != nullptr && p > 0.f) ? 1 : 0;
   rp_p.out = out;
-  rp_p.keep = keep;
+  rp_p.keep_out = keep_out;
   rp_p.M = (int)M;
   rp_p.C = (int)C;
   rp_p.out_scale = out_scale;
-  rp_p.dropout = keep != nullptr ? 1 : 0;
+  rp_p.dropout = p > 0.f ? 1 : 0;
+  rp_p.seed = seed;
+  rp_p.offset = offset;
+  rp_p.thresh14 = static_cast<uint32_t>(p * 16384.0f + 0.5f);
   const bool bf = dtype == kDtypeBf16;
 #define RP_CASE(BF, RP) return launch_rowproj_t<BF, RP>(tmAct, tmP, tmXd, rp_p, stream);
   if (bf) {
@@ -470,10 +467,10 @@ int lora_linear_fwd(const void* X, const void* W, const void* bias, const float*
   const int rp = rpad_of(r);
   const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
 
-  uint8_t* keep = p > 0.f ? keep_mask : nullptr;
-  if (phase_on(kPhasePack) && launch_pack(A, B, ws, w, K, N, r, scaling, dtype, keep, M, p, seed, offset, sms, stream))
+  if (phase_on(kPhasePack) && launch_pack(A, B, ws, w, K, N, r, scaling, dtype, stream)) return 1;
+  if (phase_on(kPhaseRowProj) &&
+      launch_rowproj(X, ws + w.a16, H, keep_mask, Xd, M, K, rp, dtype, inv_keep, p, seed, offset, stream))
     return 1;
-  if (phase_on(kPhaseRowProj) && launch_rowproj(X, ws + w.a16, H, keep, Xd, M, K, rp, dtype, inv_keep, stream)) return 1;
   if (!phase_on(kPhaseGemm)) return 0;
   GemmArgs g{};
   g.A1 = X;
@@ -508,10 +505,10 @@ int lora_linear_bwd(const void* dY, const void* X, const void* W, const float* A
   void* dH = ws + w.dh;
   float* partial = reinterpret_cast<float*>(ws + w.partial);
 
-  if (phase_on(kPhasePack) && launch_pack(A, B, ws, w, K, N, r, scaling, dtype, nullptr, 0, 0.f, 0, 0, sms, stream))
-    return 1;
+  if (phase_on(kPhasePack) && launch_pack(A, B, ws, w, K, N, r, scaling, dtype, stream)) return 1;
   // dH[M, rp] = dY (sB)
-  if (phase_on(kPhaseRowProj) && launch_rowproj(dY, ws + w.sb16t, dH, nullptr, nullptr, M, N, rp, dtype, 1.f, stream))
+  if (phase_on(kPhaseRowProj) &&
+      launch_rowproj(dY, ws + w.sb16t, dH, nullptr, nullptr, M, N, rp, dtype, 1.f, 0.f, 0, 0, stream))
     return 1;
   if (dX && phase_on(kPhaseGemm)) {
     GemmArgs g{};

@@ -65,8 +65,7 @@ __device__ __forceinline__ uint4 apply_keep(uint4 x, uint32_t bits) {
 // ---------------------------------------------------------------------------
 // pack: fp32 masters A[r,K], B[N,r] -> 16-bit operands in the four layouts the
 // kernels read (zero padded to r_pad; the scaling s is folded into B); also clears
-// the arrival counters of the column projections that follow in the same call and,
-// for a forward with dropout, draws the keep-bits of X (Philox4x32-10).
+// the arrival counters of the column projections that follow in the same call.
 //   a16 [r_pad,K]   a16t [K,r_pad]   sb16 [N,r_pad]   sb16t [r_pad,N]
 // ---------------------------------------------------------------------------
 template <typename T>
@@ -83,26 +82,9 @@ __device__ __forceinline__ __half cvt16<__half>(float v) {
 template <typename T>
 __global__ void pack_adapters_kernel(const float* __restrict__ A, const float* __restrict__ B, T* __restrict__ a16,
                                      T* __restrict__ a16t, T* __restrict__ sb16, T* __restrict__ sb16t, int K, int N,
-                                     int r, int r_pad, float s, unsigned int* __restrict__ counters, int n_counters,
-                                     uint8_t* __restrict__ keep_out, long long keep_groups, uint64_t seed,
-                                     uint64_t offset, uint32_t thresh14) {
+                                     int r, int r_pad, float s, unsigned int* __restrict__ counters, int n_counters) {
   // the column-projection kernels of the same call count arrivals here (must start at zero)
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_counters; i += gridDim.x * blockDim.x) counters[i] = 0u;
-  // Forward with dropout: draw the keep-bits of every 8-element group of X here -- one Philox call
-  // per thread at full occupancy (no smem, few registers), instead of inside the row projection
-  // whose warps are few and latency-bound.  keep_out[g] = bits of group g (byte index == group).
-  if (keep_out != nullptr) {
-    const PhiloxKeys rk = philox_round_keys(seed);
-    const uint32_t th2 = dropout_thresh_half2(thresh14);
-    const uint32_t off_lo = static_cast<uint32_t>(offset), off_hi = static_cast<uint32_t>(offset >> 32);
-    for (long long g = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; g < keep_groups;
-         g += static_cast<long long>(gridDim.x) * blockDim.x) {
-      uint32_t m4[4];
-      keep_out[g] = static_cast<uint8_t>(
-          dropout_keep_masks(static_cast<uint32_t>(g), static_cast<uint32_t>(static_cast<uint64_t>(g) >> 32), off_lo,
-                             off_hi, rk, th2, m4));
-    }
-  }
   const long long na = static_cast<long long>(r_pad) * K;
   const long long nb = static_cast<long long>(N) * r_pad;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < na + nb;
@@ -125,10 +107,10 @@ __global__ void pack_adapters_kernel(const float* __restrict__ A, const float* _
 // ---------------------------------------------------------------------------
 // rowproj: Out[M, kRPad] = out_scale * (keep .* Act)[M, C] * P[kRPad, C]^T
 // One CTA per 64 rows.  Warp 8 is the TMA producer; consumer warps w and w+4 form a pair
-// that owns rows 16(w%4)..+15: each masks half of the slab's 16-byte chunks (keep-bytes drawn
-// by the pack kernel, fetched one K-block ahead, expanded to AND-masks through a 256-entry
-// smem table), the pair meets on a named barrier, then each takes half of the tile's k16
-// steps.  The two partial accumulators are summed through shared memory at the end.
+// that owns rows 16(w%4)..+15: each masks half of the slab's 16-byte chunks (one Philox call
+// per 8 elements, drawn BEFORE waiting for the tile so the ALU work hides under the TMA
+// latency), the pair meets on a named barrier, then each takes half of the tile's k16 steps.
+// The two partial accumulators are summed through shared memory at the end.
 // ---------------------------------------------------------------------------
 constexpr int RP_BM = 64;
 constexpr int RP_BK = 64;
@@ -142,16 +124,18 @@ __host__ __device__ constexpr int rp_slot_bytes() {
 }
 template <int kRPad>
 __host__ __device__ constexpr int rp_smem_bytes() {
-  return RP_STAGES * rp_slot_bytes<kRPad>() + RP_BM * kRPad * 4 + 4096 + 1024 + 256;
+  return RP_STAGES * rp_slot_bytes<kRPad>() + RP_BM * kRPad * 4 + 1024 + 256;
 }
 
 struct RowProjParams {
   void* out;  // [M, kRPad] 16-bit
-  const uint8_t* keep;  // [M, C/8] keep-bits (dropout on) or null
+  uint8_t* keep_out;  // [M, C/8] or null
   int M, C;
   float out_scale;
   int dropout;  // 0/1
   int store_xd;  // 1: TMA-store the masked tiles (keep .* Act, unscaled) through tmXd
+  uint64_t seed, offset;
+  uint32_t thresh14;  // round(p * 16384)
 };
 
 template <bool kBf16, int kRPad>
@@ -163,8 +147,7 @@ __global__ void __launch_bounds__(RP_THREADS)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   float* sred = reinterpret_cast<float*>(smem + RP_STAGES * SLOT);  // [64 rows][kRPad] pair reduction
-  uint4* lut = reinterpret_cast<uint4*>(smem + RP_STAGES * SLOT + RP_BM * kRPad * 4);  // keep-byte -> 4 AND-masks
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + RP_STAGES * SLOT + RP_BM * kRPad * 4 + 4096);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + RP_STAGES * SLOT + RP_BM * kRPad * 4);
   uint64_t* empty = full + RP_STAGES;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -177,14 +160,6 @@ __global__ void __launch_bounds__(RP_THREADS)
       mbar_init(&empty[i], RP_CONSUMERS);
     }
     fence_barrier_init();
-  }
-  if (p.dropout && threadIdx.x < 256) {
-    const uint32_t b = threadIdx.x;
-    uint32_t w[4];
-#pragma unroll
-    for (int e = 0; e < 4; ++e)
-      w[e] = (((b >> (2 * e)) & 1u) ? 0x0000FFFFu : 0u) | (((b >> (2 * e + 1)) & 1u) ? 0xFFFF0000u : 0u);
-    lut[b] = make_uint4(w[0], w[1], w[2], w[3]);
   }
   __syncthreads();
 
@@ -216,31 +191,40 @@ __global__ void __launch_bounds__(RP_THREADS)
     for (int e = 0; e < 4; ++e) acc[n][e] = 0.f;
 
   const int keep_ld = p.C >> 3;
-  // Per-lane byte offsets of this warp's two chunks in the keep-bit array: chunk (m, c) lives at
-  // m*(C/8) + c/8, i.e. a per-lane base plus 8 per K-block.
-  size_t kbase[2] = {0, 0};
+  // Per-lane constants of the dropout draw: the Philox counter of chunk (m, c) is the group index
+  // g = m*(C/8) + c/8, i.e. a per-lane base plus 8 per K-block.
+  PhiloxKeys rk;
+  uint64_t gbase[2] = {0, 0};
   bool row_ok[2] = {false, false};
+  const uint32_t thresh2 = dropout_thresh_half2(p.thresh14);
+  const uint32_t off_lo = static_cast<uint32_t>(p.offset), off_hi = static_cast<uint32_t>(p.offset >> 32);
   if (p.dropout) {
+    rk = philox_round_keys(p.seed);
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
       const int idx = half * 64 + lane + 32 * i;
       const int m = m0 + slab * 16 + (idx >> 3);
       row_ok[i] = m < p.M;
-      kbase[i] = static_cast<size_t>(m) * static_cast<size_t>(keep_ld) + static_cast<size_t>(idx & 7);
+      gbase[i] = static_cast<uint64_t>(m) * static_cast<uint64_t>(keep_ld) + static_cast<uint64_t>(idx & 7);
     }
   }
-  auto load_bits = [&](int kb, uint32_t (&b)[2]) {
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      const int c8 = kb * (RP_BK / 8) + ((half * 64 + lane + 32 * i) & 7);  // chunk column = c/8
-      b[i] = (row_ok[i] && c8 < keep_ld) ? __ldg(p.keep + kbase[i] + static_cast<size_t>(kb) * (RP_BK / 8)) : 0xFFu;
-    }
-  };
-  uint32_t bits[2] = {0xFFu, 0xFFu}, bits_next[2] = {0xFFu, 0xFFu};
-  if (p.dropout && nk > 0) load_bits(0, bits);
   uint32_t stage = 0, phase = 0;
   for (int kb = 0; kb < nk; ++kb) {
-    if (p.dropout && kb + 1 < nk) load_bits(kb + 1, bits_next);  // one K-block ahead of its use
+    // keep-masks of this warp's 2 chunks per lane: independent of the data, so drawn first
+    uint32_t bits[2] = {0xFFu, 0xFFu};
+    uint32_t kmask[2][4];
+    if (p.dropout) {
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int c8 = kb * (RP_BK / 8) + ((half * 64 + lane + 32 * i) & 7);  // chunk column = c/8
+        if (row_ok[i] && c8 < keep_ld) {
+          const uint64_t g = gbase[i] + static_cast<uint64_t>(kb * (RP_BK / 8));
+          bits[i] = dropout_keep_masks(static_cast<uint32_t>(g), static_cast<uint32_t>(g >> 32), off_lo, off_hi, rk,
+                                       thresh2, kmask[i]);
+          p.keep_out[g] = static_cast<uint8_t>(bits[i]);  // byte index == group index
+        }
+      }
+    }
     mbar_wait(&full[stage], phase, 12);
     uint8_t* act = smem + stage * SLOT;
     uint8_t* pt = act + RP_ACT_BYTES;
@@ -251,14 +235,11 @@ __global__ void __launch_bounds__(RP_THREADS)
         const int R = slab * 16 + (idx >> 3), ch = idx & 7;
         if (bits[i] != 0xFFu) {
           uint4* ptr = reinterpret_cast<uint4*>(act + R * 128 + ((ch ^ (R & 7)) << 4));
-          const uint4 km = lut[bits[i]];
           uint4 x = *ptr;
-          x.x &= km.x; x.y &= km.y; x.z &= km.z; x.w &= km.w;
+          x.x &= kmask[i][0]; x.y &= kmask[i][1]; x.z &= kmask[i][2]; x.w &= kmask[i][3];
           *ptr = x;
         }
       }
-      bits[0] = bits_next[0];
-      bits[1] = bits_next[1];
       fence_proxy_async_smem();  // in-place writes -> visible to the TMA store / next TMA load
       asm volatile("bar.sync %0, 64;" ::"r"(1 + slab) : "memory");  // the pair's slab is fully masked
       if (p.store_xd && half == 0 && lane == 0) {
