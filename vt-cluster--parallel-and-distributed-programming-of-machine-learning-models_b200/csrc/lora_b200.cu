@@ -196,8 +196,8 @@ int launch_pack(const float* A, const float* B, uint8_t* ws, const Workspace& w,
 template <bool BF, int RP>
 int launch_rowproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmP, const CUtensorMap& tmXd,
                      const skinny::RowProjParams& p, cudaStream_t stream) {
-  const int grid = (p.M + skinny::RP_BM - 1) / skinny::RP_BM;
-  skinny::rowproj_kernel<BF, RP><<<grid, skinny::RP_THREADS, skinny::rp_smem_bytes<RP>(), stream>>>(tmAct, tmP, tmXd, p);
+  const int grid = (p.M + skinny::rp_rows(RP) - 1) / skinny::rp_rows(RP);
+  skinny::rowproj_kernel<BF, RP><<<grid, skinny::rp_threads(RP), skinny::rp_smem_bytes<RP>(), stream>>>(tmAct, tmP, tmXd, p);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -206,7 +206,7 @@ int launch_rowproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmP, const CUt
 int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out, void* xd_out, int64_t M, int64_t C,
                    int rp, int dtype, float out_scale, float p, uint64_t seed, uint64_t offset, cudaStream_t stream) {
   CUtensorMap tmAct, tmP, tmXd;
-  if (make_tmap(&tmAct, act, dtype, C, M, C, skinny::RP_BK, skinny::RP_BM, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj act")) return 1;
+  if (make_tmap(&tmAct, act, dtype, C, M, C, skinny::RP_BK, skinny::rp_rows(rp), CU_TENSOR_MAP_SWIZZLE_128B, "rowproj act")) return 1;
   if (make_tmap(&tmP, P, dtype, C, rp, C, skinny::RP_BK, rp, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj P")) return 1;
   if (xd_out) {
     if (make_tmap(&tmXd, xd_out, dtype, C, M, C, skinny::RP_BK, 16, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj Xd")) return 1;

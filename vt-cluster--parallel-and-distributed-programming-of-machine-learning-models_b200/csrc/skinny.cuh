@@ -106,25 +106,32 @@ __global__ void pack_adapters_kernel(const float* __restrict__ A, const float* _
 
 // ---------------------------------------------------------------------------
 // rowproj: Out[M, kRPad] = out_scale * (keep .* Act)[M, C] * P[kRPad, C]^T
-// One CTA per 64 rows.  Warp 8 is the TMA producer; consumer warps w and w+4 form a pair
-// that owns rows 16(w%4)..+15: each masks half of the slab's 16-byte chunks (one Philox call
-// per 8 elements, drawn BEFORE waiting for the tile so the ALU work hides under the TMA
-// latency), the pair meets on a named barrier, then each takes half of the tile's k16 steps.
-// The two partial accumulators are summed through shared memory at the end.
+// One CTA per 16*SLABS rows (SLABS by padded rank, below).  The last warp is the TMA producer;
+// consumer warps w and w+SLABS form a pair that owns rows 16(w%SLABS)..+15: each masks half of the
+// slab's 16-byte chunks (one Philox call per 8 elements, drawn BEFORE waiting for the tile so the
+// ALU work hides under the TMA latency), the pair meets on a named barrier, then each takes half
+// of the tile's k16 steps.  The two partial accumulators are summed through shared memory at the end.
 // ---------------------------------------------------------------------------
-constexpr int RP_BM = 64;
+// ---------------------------------------------------------------------------
+// 16-row slabs per CTA: one for the narrow ranks (1024 small CTAs at M = 16384 spread evenly over
+// 148 SMs and nine fit per SM -- the dropout draw is ALU-bound, balance and occupancy matter), more
+// for wide ranks so that the P tile, which every CTA re-reads from L2, stays small next to Act's.
+__host__ __device__ constexpr int rp_slabs(int rpad) { return rpad <= 16 ? 1 : (rpad <= 32 ? 2 : 4); }
+__host__ __device__ constexpr int rp_rows(int rpad) { return 16 * rp_slabs(rpad); }
+__host__ __device__ constexpr int rp_threads(int rpad) { return (2 * rp_slabs(rpad) + 1) * 32; }
 constexpr int RP_BK = 64;
 constexpr int RP_STAGES = 6;
-constexpr int RP_ACT_BYTES = RP_BM * 128;  // 8 KiB
-constexpr int RP_CONSUMERS = 8;
-constexpr int RP_THREADS = (RP_CONSUMERS + 1) * 32;
+template <int kRPad>
+__host__ __device__ constexpr int rp_act_bytes() {
+  return ((rp_rows(kRPad) * 128 + 1023) / 1024) * 1024;
+}
 template <int kRPad>
 __host__ __device__ constexpr int rp_slot_bytes() {
-  return RP_ACT_BYTES + ((kRPad * 128 + 1023) / 1024) * 1024;
+  return rp_act_bytes<kRPad>() + ((kRPad * 128 + 1023) / 1024) * 1024;
 }
 template <int kRPad>
 __host__ __device__ constexpr int rp_smem_bytes() {
-  return RP_STAGES * rp_slot_bytes<kRPad>() + RP_BM * kRPad * 4 + 1024 + 256;
+  return RP_STAGES * rp_slot_bytes<kRPad>() + rp_rows(kRPad) * kRPad * 4 + 1024 + 256;
 }
 
 struct RowProjParams {
@@ -139,11 +146,15 @@ struct RowProjParams {
 };
 
 template <bool kBf16, int kRPad>
-__global__ void __launch_bounds__(RP_THREADS)
+__global__ void __launch_bounds__(rp_threads(kRPad))
     rowproj_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constant__ CUtensorMap tmP,
                    const __grid_constant__ CUtensorMap tmXd, const RowProjParams p) {
   constexpr int SLOT = rp_slot_bytes<kRPad>();
   constexpr int NB = kRPad / 8;
+  constexpr int SLABS = rp_slabs(kRPad);
+  constexpr int RP_BM = rp_rows(kRPad);
+  constexpr int RP_CONSUMERS = 2 * SLABS;
+  constexpr int RP_ACT_BYTES = rp_act_bytes<kRPad>();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   float* sred = reinterpret_cast<float*>(smem + RP_STAGES * SLOT);  // [64 rows][kRPad] pair reduction
@@ -169,7 +180,7 @@ __global__ void __launch_bounds__(RP_THREADS)
       for (int kb = 0; kb < nk; ++kb) {
         mbar_wait(&empty[stage], phase ^ 1, 11);
         uint8_t* act = smem + stage * SLOT;
-        mbar_arrive_expect_tx(&full[stage], RP_ACT_BYTES + kRPad * 128);
+        mbar_arrive_expect_tx(&full[stage], RP_BM * 128 + kRPad * 128);
         tma_load_2d(act, &tmAct, &full[stage], kb * RP_BK, m0);
         tma_load_2d(act + RP_ACT_BYTES, &tmP, &full[stage], kb * RP_BK, 0);
         if (++stage == RP_STAGES) {
@@ -182,8 +193,8 @@ __global__ void __launch_bounds__(RP_THREADS)
     return;
   }
 
-  const int slab = warp & 3;   // 16-row slab of the tile
-  const int half = warp >> 2;  // which half of the slab's chunks / k-steps this warp takes
+  const int slab = warp % SLABS;  // 16-row slab of the tile
+  const int half = warp / SLABS;  // which half of the slab's chunks / k-steps this warp takes
   float acc[NB][4];
 #pragma unroll
   for (int n = 0; n < NB; ++n)
