@@ -32,6 +32,17 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 }
 
 // ---------------------------------------------------------------------------
+// Programmatic dependent launch: every kernel of a forward/backward call is launched with the
+// programmatic-stream-serialization attribute, signals `launch_dependents` at once (the next
+// kernel's CTAs may take over SMs as ours retire and run their set-up: barrier init, TMEM
+// allocation, tensor-map prefetch) and executes `wait` before its first access to memory that an
+// earlier kernel of the stream wrote (wait returns when the preceding grid has fully completed
+// and its writes are visible).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// ---------------------------------------------------------------------------
 // mbarrier
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {

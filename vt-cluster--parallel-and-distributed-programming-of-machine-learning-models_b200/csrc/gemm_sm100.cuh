@@ -159,10 +159,12 @@ __global__ void __launch_bounds__(THREADS, 1)
       tmem_relinquish();
     }
   }
+  pdl_launch_dependents();
   tc_fence_before();
   if constexpr (kPair) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // everything above overlapped the previous kernel's tail; its outputs are needed from here on
 
   // Tiles are BM*CTAS rows tall; a cluster (or lone CTA) walks them persistently.
   constexpr int TILE_M = BM * C::CTAS;

@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <utility>
 
 #include "gemm_sm100.cuh"
 #include "lora_b200.h"
@@ -79,6 +80,33 @@ CUtensorMapSwizzle swizzle_for_row_bytes(int bytes) {
 enum : int { kPhasePack = 1, kPhaseRowProj = 2, kPhaseGemm = 4, kPhaseColProj = 8, kPhaseAll = 15 };
 std::atomic<int> g_phase_mask{kPhaseAll};
 inline bool phase_on(int ph) { return (g_phase_mask.load(std::memory_order_relaxed) & ph) != 0; }
+
+// Launch with programmatic stream serialization (see common.cuh: pdl_wait / pdl_launch_dependents) and an
+// optional cluster width.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, int cluster,
+                       Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  int n = 0;
+  attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[n].val.programmaticStreamSerializationAllowed = 1;
+  ++n;
+  if (cluster > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = cluster;
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
 
 constexpr int kMaxDevices = 64;
 struct DeviceInfo {
@@ -181,14 +209,14 @@ int launch_pack(const float* A, const float* B, uint8_t* ws, const Workspace& w,
   const long long total = static_cast<long long>(rp) * (K + N);
   const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, 2048));
   if (dtype == kDtypeBf16)
-    skinny::pack_adapters_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(
-        A, B, (__nv_bfloat16*)(ws + w.a16), (__nv_bfloat16*)(ws + w.a16t), (__nv_bfloat16*)(ws + w.sb16),
-        (__nv_bfloat16*)(ws + w.sb16t), (int)K, (int)N, r, rp, s, (unsigned int*)(ws + w.counters), 2 * kMaxColTiles);
+    CUDA_TRY(launch_pdl(skinny::pack_adapters_kernel<__nv_bfloat16>, dim3(grid), dim3(256), 0, stream, 1, A, B,
+                        (__nv_bfloat16*)(ws + w.a16), (__nv_bfloat16*)(ws + w.a16t), (__nv_bfloat16*)(ws + w.sb16),
+                        (__nv_bfloat16*)(ws + w.sb16t), (int)K, (int)N, r, rp, s, (unsigned int*)(ws + w.counters),
+                        2 * kMaxColTiles));
   else
-    skinny::pack_adapters_kernel<__half><<<grid, 256, 0, stream>>>(A, B, (__half*)(ws + w.a16), (__half*)(ws + w.a16t),
-                                                                    (__half*)(ws + w.sb16), (__half*)(ws + w.sb16t),
-                                                                    (int)K, (int)N, r, rp, s,
-                                                                    (unsigned int*)(ws + w.counters), 2 * kMaxColTiles);
+    CUDA_TRY(launch_pdl(skinny::pack_adapters_kernel<__half>, dim3(grid), dim3(256), 0, stream, 1, A, B,
+                        (__half*)(ws + w.a16), (__half*)(ws + w.a16t), (__half*)(ws + w.sb16), (__half*)(ws + w.sb16t),
+                        (int)K, (int)N, r, rp, s, (unsigned int*)(ws + w.counters), 2 * kMaxColTiles));
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -197,8 +225,8 @@ template <bool BF, int RP>
 int launch_rowproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmP, const CUtensorMap& tmXd,
                      const skinny::RowProjParams& p, cudaStream_t stream) {
   const int grid = (p.M + skinny::rp_rows(RP) - 1) / skinny::rp_rows(RP);
-  skinny::rowproj_kernel<BF, RP><<<grid, skinny::rp_threads(RP), skinny::rp_smem_bytes<RP>(), stream>>>(tmAct, tmP, tmXd, p);
-  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(launch_pdl(skinny::rowproj_kernel<BF, RP>, dim3(grid), dim3(skinny::rp_threads(RP)), skinny::rp_smem_bytes<RP>(),
+                      stream, 1, tmAct, tmP, tmXd, p));
   return 0;
 }
 
@@ -256,9 +284,8 @@ int launch_colproj_t(const CUtensorMap (&tmAct)[2], const CUtensorMap (&tmSmall)
     gy = std::max(gy, pp.prob[i].splits);
   }
   dim3 grid(gx, gy, njobs);
-  skinny::colproj_kernel<BF, RP><<<grid, skinny::CP_THREADS, skinny::cp_smem_bytes<RP>(), stream>>>(
-      tmAct[0], tmSmall[0], tmAct[1], tmSmall[1], pp);
-  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(launch_pdl(skinny::colproj_kernel<BF, RP>, grid, dim3(skinny::CP_THREADS), skinny::cp_smem_bytes<RP>(), stream, 1,
+                      tmAct[0], tmSmall[0], tmAct[1], tmSmall[1], pp));
   return 0;
 }
 
@@ -332,19 +359,8 @@ bool pair_mode_allowed() {
 template <bool kMasked, bool kPair>
 int launch_gemm_t(const CUtensorMap& tmA1, const CUtensorMap& tmB1, const CUtensorMap& tmA2, const CUtensorMap& tmB2,
                   const CUtensorMap& tmD, const gemm::Params& p, int grid, cudaStream_t stream) {
-  cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(gemm::THREADS);
-  cfg.dynamicSmemBytes = gemm::SMEM_BYTES;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = kPair ? 2 : 1;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  CUDA_TRY(cudaLaunchKernelEx(&cfg, gemm::gemm_lora_kernel<kMasked, kPair>, tmA1, tmB1, tmA2, tmB2, tmD, p));
+  CUDA_TRY(launch_pdl(gemm::gemm_lora_kernel<kMasked, kPair>, dim3(grid), dim3(gemm::THREADS), gemm::SMEM_BYTES, stream,
+                      kPair ? 2 : 1, tmA1, tmB1, tmA2, tmB2, tmD, p));
   return 0;
 }
 

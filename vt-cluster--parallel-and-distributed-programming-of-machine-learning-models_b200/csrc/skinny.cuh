@@ -83,6 +83,8 @@ template <typename T>
 __global__ void pack_adapters_kernel(const float* __restrict__ A, const float* __restrict__ B, T* __restrict__ a16,
                                      T* __restrict__ a16t, T* __restrict__ sb16, T* __restrict__ sb16t, int K, int N,
                                      int r, int r_pad, float s, unsigned int* __restrict__ counters, int n_counters) {
+  pdl_launch_dependents();
+  pdl_wait();  // the workspace may still be in use by the previous call's kernels
   // the column-projection kernels of the same call count arrivals here (must start at zero)
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_counters; i += gridDim.x * blockDim.x) counters[i] = 0u;
   const long long na = static_cast<long long>(r_pad) * K;
@@ -171,7 +173,9 @@ __global__ void __launch_bounds__(rp_threads(kRPad))
     }
     fence_barrier_init();
   }
+  pdl_launch_dependents();
   __syncthreads();
+  pdl_wait();
 
   if (warp == RP_CONSUMERS) {
     if (lane == 0) {
@@ -396,7 +400,9 @@ __global__ void __launch_bounds__(CP_THREADS)
     fence_barrier_init();
   }
   for (int i = threadIdx.x; i < COLS * kRPad; i += CP_THREADS) sout[i] = 0.f;
+  pdl_launch_dependents();
   __syncthreads();
+  pdl_wait();
 
   if (warp == CP_CONSUMERS) {
     if (lane == 0) {
