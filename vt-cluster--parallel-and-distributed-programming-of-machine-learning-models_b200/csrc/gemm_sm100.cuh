@@ -382,7 +382,68 @@ __global__ void __launch_bounds__(THREADS, 1)
       tc_fence_after();
 
       const bool warp_rows_ok = rbase < p.M;  // else this warp's 32 rows are all padding
-      for (int cb = 0; cb < BN / 64 && warp_rows_ok; ++cb) {
+      if constexpr (!kMasked) {
+        // Plain epilogue, software-pipelined: the TMEM load of the next 32-column chunk is in flight
+        // while the current one is biased, converted and staged (two register sets alternate).
+        if (warp_rows_ok) {
+          const int nchunks = (min(BN, p.N - n_blk * BN) + 31) / 32;  // warp-uniform, >= 1
+          const uint32_t tbase = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + buf * BN;
+          auto emit = [&](uint32_t (&v)[32], int c, int h, uint8_t* sdst) {
+            if (p.bias != nullptr) {
+              const uint4* bp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.bias) + c);
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                if (c + q * 8 < p.N) {
+                  const uint4 bw = __ldg(bp + q);
+                  const uint32_t w4[4] = {bw.x, bw.y, bw.z, bw.w};
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) {
+                    const float2 f = unpack2(w4[e], dtype);
+                    v[q * 8 + e * 2] = __float_as_uint(__uint_as_float(v[q * 8 + e * 2]) + f.x);
+                    v[q * 8 + e * 2 + 1] = __float_as_uint(__uint_as_float(v[q * 8 + e * 2 + 1]) + f.y);
+                  }
+                }
+              }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              uint4 o;
+              o.x = pack2(__uint_as_float(v[q * 8 + 0]), __uint_as_float(v[q * 8 + 1]), dtype);
+              o.y = pack2(__uint_as_float(v[q * 8 + 2]), __uint_as_float(v[q * 8 + 3]), dtype);
+              o.z = pack2(__uint_as_float(v[q * 8 + 4]), __uint_as_float(v[q * 8 + 5]), dtype);
+              o.w = pack2(__uint_as_float(v[q * 8 + 6]), __uint_as_float(v[q * 8 + 7]), dtype);
+              const int chunk = h * 4 + q;
+              *reinterpret_cast<uint4*>(sdst + ((chunk ^ (lane & 7)) << 4)) = o;
+            }
+          };
+          uint32_t va[32], vb[32];
+          tmem_ld_32x32b_x32(tbase, va);
+          for (int ci = 0; ci < nchunks; ci += 2) {
+            // the staging buffer we are about to overwrite must have been read by its TMA store
+            if (lane == 0) bulk_wait_group_read<1>();
+            __syncwarp();
+            uint8_t* sdst = my_stage + sbuf * EPI_BUF_BYTES + lane * 128;
+            const int col0 = n_blk * BN + ci * 32;
+            const bool has_b = ci + 1 < nchunks;
+            tmem_ld_wait();
+            if (has_b) tmem_ld_32x32b_x32(tbase + (ci + 1) * 32, vb);
+            emit(va, col0, 0, sdst);
+            if (has_b) {
+              tmem_ld_wait();
+              if (ci + 2 < nchunks) tmem_ld_32x32b_x32(tbase + (ci + 2) * 32, va);
+              emit(vb, col0 + 32, 1, sdst);
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&tmD, my_stage + sbuf * EPI_BUF_BYTES, col0, rbase);
+              bulk_commit_group();
+            }
+            sbuf ^= 1u;
+          }
+        }
+      }
+      for (int cb = 0; cb < BN / 64 && warp_rows_ok && kMasked; ++cb) {
         const int col0 = n_blk * BN + cb * 64;
         if (col0 >= p.N) break;  // warp-uniform
         // the staging buffer we are about to overwrite must have been read by its TMA store
