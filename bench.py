@@ -289,55 +289,25 @@ def run_point(a, pkg, rank, world, device, with_e2e=True):
         hdb = torch.empty(N, r).pin_memory()
         Ap, Bp = A.clone().requires_grad_(True), B.clone().requires_grad_(True)
 
-        # Host buffers in, host buffers out, every step; copies run on their own streams so that the
-        # H2D of step i+1, the kernels of step i and the D2H of step i-1 overlap (PCIe is full duplex).
-        s_in, s_out = torch.cuda.Stream(device=device), torch.cuda.Stream(device=device)
-        cur = torch.cuda.current_stream(device)
-        dx_in = [torch.empty(M, K, dtype=dtype, device=device) for _ in range(2)]
-        dy_in = [torch.empty(M, N, dtype=dtype, device=device) for _ in range(2)]
-        ev_in = [torch.cuda.Event() for _ in range(2)]
-        ev_done = [torch.cuda.Event() for _ in range(2)]   # compute of slot finished (inputs reusable, outputs ready)
-        ev_out = [torch.cuda.Event() for _ in range(2)]    # D2H of slot finished (output tensors reusable)
-        outs = [None, None]
-
-        def e2e_step(i):
-            sl = i & 1
-            with torch.cuda.stream(s_in):
-                s_in.wait_event(ev_done[sl])  # previous use of this slot's device inputs is over
-                dx_in[sl].copy_(hx, non_blocking=True)
-                dy_in[sl].copy_(hdy, non_blocking=True)
-                ev_in[sl].record(s_in)
-            cur.wait_event(ev_in[sl])
-            cur.wait_event(ev_out[sl])  # slot's previous outputs have left the device
-            xd = dx_in[sl].requires_grad_(True)
+        def e2e_step():
+            xd = hx.to(device, non_blocking=True).requires_grad_(True)
+            dyd = hdy.to(device, non_blocking=True)
             y = pkg.fused_lora_linear(xd, W, b, Ap, Bp, s, p=p, training=True, w_is_KN=a.conv1d)
-            y.backward(dy_in[sl])
-            outs[sl] = (y.detach(), xd.grad, Ap.grad, Bp.grad)
+            y.backward(dyd)
+            hy.copy_(y.detach(), non_blocking=True)
+            hdx.copy_(xd.grad, non_blocking=True)
+            hda.copy_(Ap.grad, non_blocking=True)
+            hdb.copy_(Bp.grad, non_blocking=True)
             Ap.grad = None
             Bp.grad = None
-            dx_in[sl].requires_grad_(False)
-            dx_in[sl].grad = None
-            ev_done[sl].record(cur)
-            with torch.cuda.stream(s_out):
-                s_out.wait_event(ev_done[sl])
-                yy, gx, ga, gb = outs[sl]
-                hy.copy_(yy, non_blocking=True)
-                hdx.copy_(gx, non_blocking=True)
-                hda.copy_(ga, non_blocking=True)
-                hdb.copy_(gb, non_blocking=True)
-                for t in (yy, gx, ga, gb):
-                    t.record_stream(s_out)
-                ev_out[sl].record(s_out)
 
         e2e_steps = max(5, min(a.steps, 20))
-        for i in range(4):
-            e2e_step(i)
-        s_out.synchronize()
+        for _ in range(3):
+            e2e_step()
         barrier()
         e0.record()
-        for i in range(e2e_steps):
-            e2e_step(i)
-        cur.wait_stream(s_out)  # the timed region ends when the last result is back in host memory
+        for _ in range(e2e_steps):
+            e2e_step()
         e1.record()
         barrier()
         e2e_ms = e0.elapsed_time(e1) / e2e_steps
