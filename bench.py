@@ -52,6 +52,9 @@ def parse():
     ap.add_argument("--seq", type=int, default=0, help="model workloads: sequence length")
     ap.add_argument("--layers", type=int, default=0, help="model workloads: override the number of layers (debug)")
     ap.add_argument("--no-ckpt", action="store_true", help="model workloads: gradient checkpointing off")
+    ap.add_argument("--stock-head", action="store_true",
+                    help="model workloads: keep torch's lm_head matmul and fp32 cross-entropy (default: lm_head through "
+                         "the tcgen05 GEMM + fused cross-entropy, SURVEY 8f rows N2/N3)")
     return ap.parse_args()
 
 
@@ -358,7 +361,8 @@ def model_spec(a):
 def model_workload_name(a, B, S, world):
     return (f"{a.workload} architecture (random init) LoRA r=8 alpha=16 dropout=0.05 fine-tune step, "
             f"gradient checkpointing {'off' if a.no_ckpt else 'on'}, batch {B} x seq {S} per GPU, "
-            f"{'DDP over NCCL, ' if world > 1 else ''}AdamW lr 5e-5 + clip 1.0")
+            f"{'DDP over NCCL, ' if world > 1 else ''}AdamW lr 5e-5 + clip 1.0, "
+            f"{'stock torch lm_head + fp32 CE' if a.stock_head else 'lm_head on the tcgen05 GEMM + fused CE'}")
 
 
 def run_model(a, pkg, rank, world, device):
@@ -375,8 +379,12 @@ def run_model(a, pkg, rank, world, device):
     pm = pkg.get_peft_model(model, pkg.LoraConfig(r=8, lora_alpha=16, target_modules=targets, lora_dropout=0.05,
                                                   bias="none", task_type=pkg.TaskType.CAUSAL_LM))
     n_lora = len(pm.base_model.lora_layers())
+    loss_fn = None
+    if not a.stock_head:
+        pkg.frozen.accelerate_lm_head(pm)
+        loss_fn = pkg.frozen.fused_causal_lm_loss
     net = pkg.train.wrap_ddp(pm, device) if world > 1 else pm
-    tr = pkg.train.Trainer(net, pkg.train.TrainConfig(lr=5e-5, accum=1, total_steps=10 ** 6))
+    tr = pkg.train.Trainer(net, pkg.train.TrainConfig(lr=5e-5, accum=1, total_steps=10 ** 6), loss_fn=loss_fn)
     tr._ensure_sched(10 ** 6)
     net.train()
     n_batches = 4

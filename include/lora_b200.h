@@ -134,6 +134,35 @@ int lora_linear_grad_b_static(const void* dY, const void* H, float* dB, int64_t 
                               float scaling, int32_t dtype, int32_t accumulate, cudaStream_t stream);
 
 /*
+ * Un-adapted (frozen, no LoRA) projection through the same tcgen05 kernel, with leading dimensions
+ * so that outputs whose width is not a multiple of 8 can live in a padded buffer (SURVEY.md 8f row
+ * N3).  Replaces the torch F.linear / addmm calls HF makes for modules the reference does not
+ * target -- above all lm_head (768 x 50257 in distilgpt2: cuBLAS has no aligned kernel for that
+ * width).  fwd: Y[M,N] = X[M,K] W^T + bias;  bwd: dX[M,K] = dY[M,N] W (no dW: frozen).
+ * ld* are row strides in elements, multiples of 8; the weight's own row length (K for [N,K], N for
+ * w_is_KN) must be a multiple of 8; N (resp. K) itself may be ragged.
+ */
+int lora_frozen_linear_fwd(const void* X, int64_t ldx, const void* W, const void* bias, void* Y, int64_t ldy, int64_t M,
+                           int64_t K, int64_t N, int32_t dtype, int32_t w_is_KN, cudaStream_t stream);
+int lora_frozen_linear_bwd(const void* dY, int64_t lddy, const void* W, void* dX, int64_t lddx, int64_t M, int64_t K,
+                           int64_t N, int32_t dtype, int32_t w_is_KN, cudaStream_t stream);
+
+/*
+ * Token cross-entropy from 16-bit logits; replaces the fp32 logits copy +
+ * log_softmax + nll_loss that the HF causal-LM loss runs on DataCollatorForLanguageModeling labels
+ * (finetune_lora_distilgpt2.py:114) and nn.CrossEntropyLoss in finetune_lora_opt_pp.py:143-153.
+ * labels[i] (int64) is the target of row i, ignore_index where there is none -- the causal shift is
+ * applied to the labels by the caller, never to the logits.
+ * fwd: lse[i] = log sum_v exp(logits[i,v]);  loss_rows[i] = lse[i] - logits[i, labels[i]] (0 if ignored).
+ * bwd: dlogits[i,v] = (exp(logits[i,v] - lse[i]) - [v == labels[i]]) * *grad_scale (zero rows if ignored);
+ *      grad_scale is a device scalar (upstream gradient / number of counted tokens).
+ */
+int lora_ce_fwd(const void* logits, int64_t ld, const int64_t* labels, float* lse, float* loss_rows, int64_t M, int64_t V,
+                int64_t ignore_index, int32_t dtype, cudaStream_t stream);
+int lora_ce_bwd(const void* logits, int64_t ld, const int64_t* labels, const float* lse, const float* grad_scale,
+                void* dlogits, int64_t ldd, int64_t M, int64_t V, int64_t ignore_index, int32_t dtype, cudaStream_t stream);
+
+/*
  * Profiling hook, no counterpart in the reference: restricts which kernels the
  * calls above launch (bit 0 adapter packing, bit 1 rank-r row projections
  * H/dH, bit 2 the tcgen05 GEMM, bit 3 dA/dB column projections + reduce;

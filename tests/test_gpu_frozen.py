@@ -1,0 +1,94 @@
+"""SURVEY.md 8f rows N2 / N3 on the GPU: the un-adapted lm_head through the tcgen05 GEMM (ragged
+vocab, padded row stride) and the fused shifted cross-entropy, against the CPU oracle
+(torch fp32 F.linear / oracle.lora_ref.causal_lm_loss) on the same 16-bit-rounded inputs."""
+import copy
+
+import pytest
+import torch
+
+from oracle import lora_ref
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-2
+
+
+def relerr(a, ref):
+    a, ref = a.detach().float().cpu(), ref.detach().float().cpu()
+    return float((a - ref).abs().max() / ref.abs().max().clamp_min(1e-20))
+
+
+@pytest.mark.parametrize("M,K,N,dtype", [(300, 256, 1003, torch.bfloat16), (1024, 768, 50257, torch.bfloat16),
+                                         (130, 768, 512, torch.float16)])
+def test_frozen_linear_ragged_vocab(pkg, M, K, N, dtype):
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(M, K, generator=g).to(dtype)
+    W = (torch.randn(N, K, generator=g) * 0.02).to(dtype)
+    dy = torch.randn(M, N, generator=g).to(dtype)
+    lin = torch.nn.Linear(K, N, bias=False).to(dtype)
+    with torch.no_grad():
+        lin.weight.copy_(W)
+    lin.requires_grad_(False)
+    fl = pkg.frozen.FrozenLinear(lin.cuda())
+    xg = x.cuda().requires_grad_(True)
+    y = fl(xg)
+    assert y.shape == (M, N)
+    y.backward(dy.cuda())
+    ref_y = x.float() @ W.float().t()
+    ref_dx = dy.float() @ W.float()
+    assert relerr(y, ref_y) < TOL and relerr(xg.grad, ref_dx) < TOL
+    assert lin.weight.grad is None
+
+
+@pytest.mark.parametrize("B,S,V,dtype", [(2, 33, 1003, torch.bfloat16), (4, 128, 50257, torch.bfloat16),
+                                         (3, 17, 512, torch.float16)])
+def test_fused_causal_lm_loss_matches_oracle(pkg, B, S, V, dtype):
+    g = torch.Generator().manual_seed(1)
+    logits = (torch.randn(B, S, V, generator=g) * 2).to(dtype)
+    labels = torch.randint(0, V, (B, S), generator=g)
+    labels[0, 3:6] = -100  # padded positions, DataCollatorForLanguageModeling style
+    ref_in = logits.float().requires_grad_(True)
+    ref = lora_ref.causal_lm_loss(ref_in, labels)
+    (ref * 0.5).backward()
+    lg = logits.cuda().requires_grad_(True)
+    loss = pkg.frozen.fused_causal_lm_loss(lg, labels.cuda())
+    (loss * 0.5).backward()
+    assert abs(float(loss) - float(ref)) / abs(float(ref)) < 2e-3
+    assert lg.grad.shape == (B, S, V)
+    assert relerr(lg.grad, ref_in.grad) < TOL
+    assert float(lg.grad[:, -1].float().abs().max()) == 0.0  # the last position has no target
+    assert float(lg.grad[0, 2:5].float().abs().max()) == 0.0  # rows whose shifted label is -100
+
+
+def test_model_with_fast_head_and_loss_matches_stock_path(pkg):
+    """distilgpt2-style model with a ragged vocab: swapping lm_head + loss changes nothing but speed."""
+    from transformers import GPT2Config, GPT2LMHeadModel
+
+    torch.manual_seed(0)
+    base = GPT2LMHeadModel(GPT2Config(n_layer=2, n_embd=256, n_head=4, vocab_size=1003, n_positions=64,
+                                      resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0)).to(torch.bfloat16)
+    cfg = pkg.LoraConfig(r=8, lora_alpha=16, target_modules=["c_attn", "c_proj"], task_type=pkg.TaskType.CAUSAL_LM)
+    ids = torch.randint(0, 1003, (2, 48), generator=torch.Generator().manual_seed(2)).cuda()
+    res = []
+    for fast in (False, True):
+        torch.manual_seed(5)
+        pm = pkg.get_peft_model(copy.deepcopy(base), cfg).cuda()
+        with torch.no_grad():
+            for n, p in pm.named_parameters():
+                if "lora_B" in n:
+                    p.copy_(torch.randn(p.shape, generator=torch.Generator().manual_seed(3)).to(p.device) * 0.02)
+        if fast:
+            pkg.frozen.accelerate_lm_head(pm)
+            assert isinstance(pm.base_model.model.lm_head, pkg.frozen.FrozenLinear)
+        pm.train()
+        logits = pm(input_ids=ids).logits
+        loss = pkg.frozen.fused_causal_lm_loss(logits, ids) if fast else pkg.train.causal_lm_loss(logits, ids)
+        loss.backward()
+        res.append((float(loss), {n: p.grad.clone() for n, p in pm.named_parameters() if p.requires_grad}))
+    assert abs(res[0][0] - res[1][0]) / res[0][0] < 5e-3
+    for n in res[0][1]:
+        assert relerr(res[1][1][n], res[0][1][n]) < 5e-2, n
+
+
+def test_no_cpu_fallback(pkg):
+    with pytest.raises(RuntimeError):
+        pkg.frozen.fused_causal_lm_loss(torch.zeros(1, 4, 8), torch.zeros(1, 4, dtype=torch.long))

@@ -8,6 +8,7 @@ from . import binding  # noqa: F401  (ctypes C-ABI; fails loudly at first use if
 from . import lora  # noqa: F401
 from . import train  # noqa: F401
 from . import pipeline  # noqa: F401
+from . import frozen  # noqa: F401
 from .api import (  # noqa: F401
     LoraConfig,
     LoraModel,
@@ -22,5 +23,5 @@ from ._build import build  # noqa: F401
 
 __all__ = [
     "LoraConfig", "LoraModel", "PeftModel", "PeftModelForCausalLM", "PeftType", "TaskType", "get_peft_model",
-    "fused_lora_linear", "binding", "lora", "train", "pipeline", "build",
+    "fused_lora_linear", "binding", "lora", "train", "pipeline", "frozen", "build",
 ]

@@ -36,6 +36,13 @@ _SIGNATURES = {
     "lora_linear_base": (c_int, [c_void_p] * 4 + [c_int64, c_int64, c_int64, c_int32, c_int32, c_void_p]),
     "lora_linear_grad_b_static": (c_int, [c_void_p] * 3 + [c_int64, c_int64, c_int32, c_float, c_int32, c_int32,
                                                            c_void_p]),
+    "lora_frozen_linear_fwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64,
+                                       c_int32, c_int32, c_void_p]),
+    "lora_frozen_linear_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int32,
+                                       c_int32, c_void_p]),
+    "lora_ce_fwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int32, c_void_p]),
+    "lora_ce_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64,
+                            c_int32, c_void_p]),
     "lora_debug_set_phase_mask": (None, [c_int32]),
     "lora_dropout_keep_mask": (c_int, [c_void_p, c_int64, c_int64, c_float, c_uint64, c_uint64, c_void_p]),
 }

@@ -92,6 +92,16 @@ __device__ __forceinline__ void mma_16816_f16(float (&d)[4], const uint32_t (&a)
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
 }
 
+// Eight consecutive 16-bit bias values; `left` = columns remaining up to N (ragged N: the tail is
+// read element by element so that nothing beyond bias[N-1] is touched).
+__device__ __forceinline__ uint4 load_bias8(const uint4* p16, int left) {
+  if (left >= 8) return __ldg(p16);
+  const uint16_t* s = reinterpret_cast<const uint16_t*>(p16);
+  uint32_t w[4] = {0u, 0u, 0u, 0u};
+  for (int e = 0; e < left; ++e) w[e >> 1] |= static_cast<uint32_t>(__ldg(s + e)) << ((e & 1) * 16);
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
@@ -394,7 +404,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 #pragma unroll
               for (int q = 0; q < 4; ++q) {
                 if (c + q * 8 < p.N) {
-                  const uint4 bw = __ldg(bp + q);
+                  const uint4 bw = load_bias8(bp + q, p.N - (c + q * 8));
                   const uint32_t w4[4] = {bw.x, bw.y, bw.z, bw.w};
 #pragma unroll
                   for (int e = 0; e < 4; ++e) {
@@ -528,7 +538,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
               if (c + q * 8 < p.N) {
-                const uint4 bw = __ldg(bp + q);
+                const uint4 bw = load_bias8(bp + q, p.N - (c + q * 8));
                 const uint32_t w4[4] = {bw.x, bw.y, bw.z, bw.w};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {

@@ -12,6 +12,7 @@
 #include <string>
 #include <utility>
 
+#include "ce.cuh"
 #include "gemm_sm100.cuh"
 #include "lora_b200.h"
 #include "skinny.cuh"
@@ -332,6 +333,8 @@ int launch_colproj(const ColProjJob* jobs, int njobs, int64_t M, int r, int rp, 
 struct GemmArgs {
   const void* A1;  // [M, K1]
   const void* B1;  // [N, K1] or [K1, N]
+  int64_t lda1 = 0;  // row stride of A1 in elements (0: K1)
+  int64_t ldd = 0;   // row stride of D in elements (0: N)
   int b_mn_major;
   const void* A2;  // [M, rp] or null
   const void* B2;  // [N, rp] or null
@@ -368,7 +371,7 @@ int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, 
   const bool pair = pair_mode_allowed() && M > gemm::BM && sm_count >= 2;
   const uint32_t b_rows = pair ? gemm::BN / 2 : gemm::BN;  // rows of the B tile one CTA stages
   CUtensorMap tmA1, tmB1, tmA2, tmB2, tmD;
-  if (make_tmap(&tmA1, g.A1, dtype, K1, M, K1, gemm::BK, gemm::BM, CU_TENSOR_MAP_SWIZZLE_128B, "gemm A1")) return 1;
+  if (make_tmap(&tmA1, g.A1, dtype, K1, M, g.lda1 ? g.lda1 : K1, gemm::BK, gemm::BM, CU_TENSOR_MAP_SWIZZLE_128B, "gemm A1")) return 1;
   if (!g.b_mn_major) {
     if (make_tmap(&tmB1, g.B1, dtype, K1, N, K1, gemm::BK, b_rows, CU_TENSOR_MAP_SWIZZLE_128B, "gemm B1 (K-major)")) return 1;
   } else {
@@ -382,7 +385,7 @@ int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, 
     tmA2 = tmA1;
     tmB2 = tmB1;
   }
-  if (make_tmap(&tmD, g.D, dtype, N, M, N, 64, 32, CU_TENSOR_MAP_SWIZZLE_128B, "gemm D")) return 1;
+  if (make_tmap(&tmD, g.D, dtype, N, M, g.ldd ? g.ldd : N, 64, 32, CU_TENSOR_MAP_SWIZZLE_128B, "gemm D")) return 1;
 
   gemm::Params p;
   p.M = (int)M;
@@ -599,6 +602,74 @@ int lora_linear_grad_b_static(const void* dY, const void* H, float* dB, int64_t 
   ColProjJob job{dY, H, nullptr, reinterpret_cast<float*>(static_cast<unsigned char*>(scratch) + counter_bytes),
                  static_cast<unsigned int*>(scratch), dB, N, (long long)r, 1ll, scaling};
   return launch_colproj(&job, 1, M, r, rp, dtype, accumulate, stream);
+}
+
+int lora_frozen_linear_fwd(const void* X, int64_t ldx, const void* W, const void* bias, void* Y, int64_t ldy, int64_t M,
+                           int64_t K, int64_t N, int32_t dtype, int32_t w_is_KN, cudaStream_t stream) {
+  g_err.clear();
+  if (M <= 0 || K <= 0 || N <= 0 || M > INT32_MAX || K > INT32_MAX || N > INT32_MAX) return fail("lora_frozen_linear_fwd: bad shape");
+  if (dtype != kDtypeBf16 && dtype != kDtypeFp16) return fail("dtype must be 0 (bf16) or 1 (fp16); fp32 is not supported");
+  if (!X || !W || !Y) return fail("lora_frozen_linear_fwd: null pointer argument");
+  if (ldx < K || ldy < N || ldx % 8 || ldy % 8) return fail("lora_frozen_linear_fwd: ldx/ldy must be >= K/N and multiples of 8 elements");
+  if ((w_is_KN ? N : K) % 8) return fail("lora_frozen_linear_fwd: the weight's row length (%s) must be a multiple of 8", w_is_KN ? "N" : "K");
+  int sms = 0;
+  if (device_setup(&sms)) return 1;
+  GemmArgs g{};
+  g.A1 = X;
+  g.lda1 = ldx;
+  g.B1 = W;
+  g.b_mn_major = w_is_KN ? 1 : 0;
+  g.D = Y;
+  g.ldd = ldy;
+  g.bias = bias;
+  g.inv_keep = 1.f;
+  return launch_gemm(g, M, N, K, dtype, sms, stream);
+}
+
+int lora_frozen_linear_bwd(const void* dY, int64_t lddy, const void* W, void* dX, int64_t lddx, int64_t M, int64_t K,
+                           int64_t N, int32_t dtype, int32_t w_is_KN, cudaStream_t stream) {
+  g_err.clear();
+  if (M <= 0 || K <= 0 || N <= 0 || M > INT32_MAX || K > INT32_MAX || N > INT32_MAX) return fail("lora_frozen_linear_bwd: bad shape");
+  if (dtype != kDtypeBf16 && dtype != kDtypeFp16) return fail("dtype must be 0 (bf16) or 1 (fp16); fp32 is not supported");
+  if (!dY || !W || !dX) return fail("lora_frozen_linear_bwd: null pointer argument");
+  if (lddy < N || lddx < K || lddy % 8 || lddx % 8) return fail("lora_frozen_linear_bwd: lddy/lddx must be >= N/K and multiples of 8 elements");
+  if ((w_is_KN ? N : K) % 8) return fail("lora_frozen_linear_bwd: the weight's row length (%s) must be a multiple of 8", w_is_KN ? "N" : "K");
+  int sms = 0;
+  if (device_setup(&sms)) return 1;
+  GemmArgs g{};
+  g.A1 = dY;
+  g.lda1 = lddy;
+  g.B1 = W;
+  g.b_mn_major = w_is_KN ? 0 : 1;  // contraction runs over N
+  g.D = dX;
+  g.ldd = lddx;
+  g.inv_keep = 1.f;
+  return launch_gemm(g, M, K, N, dtype, sms, stream);
+}
+
+int lora_ce_fwd(const void* logits, int64_t ld, const int64_t* labels, float* lse, float* loss_rows, int64_t M, int64_t V,
+                int64_t ignore_index, int32_t dtype, cudaStream_t stream) {
+  g_err.clear();
+  if (!logits || !labels || !lse || !loss_rows) return fail("lora_ce_fwd: null pointer argument");
+  if (M <= 0 || V <= 0 || M > INT32_MAX || V > INT32_MAX || ld < V || ld % 8) return fail("lora_ce_fwd: need M, V > 0 and ld >= V, ld %% 8 == 0");
+  if (dtype != kDtypeBf16 && dtype != kDtypeFp16) return fail("dtype must be 0 (bf16) or 1 (fp16); fp32 is not supported");
+  CUDA_TRY(launch_pdl(ce::ce_fwd_kernel, dim3((unsigned)M), dim3(ce::THREADS), 0, stream, 1,
+                      static_cast<const uint16_t*>(logits), (long long)ld, reinterpret_cast<const long long*>(labels), lse,
+                      loss_rows, (int)V, (long long)ignore_index, (int)dtype));
+  return 0;
+}
+
+int lora_ce_bwd(const void* logits, int64_t ld, const int64_t* labels, const float* lse, const float* grad_scale,
+                void* dlogits, int64_t ldd, int64_t M, int64_t V, int64_t ignore_index, int32_t dtype, cudaStream_t stream) {
+  g_err.clear();
+  if (!logits || !labels || !lse || !grad_scale || !dlogits) return fail("lora_ce_bwd: null pointer argument");
+  if (M <= 0 || V <= 0 || M > INT32_MAX || V > INT32_MAX || ld < V || ld % 8 || ldd < V || ldd % 8)
+    return fail("lora_ce_bwd: need M, V > 0 and ld, ldd >= V, multiples of 8");
+  if (dtype != kDtypeBf16 && dtype != kDtypeFp16) return fail("dtype must be 0 (bf16) or 1 (fp16); fp32 is not supported");
+  CUDA_TRY(launch_pdl(ce::ce_bwd_kernel, dim3((unsigned)M), dim3(ce::THREADS), 0, stream, 1,
+                      static_cast<const uint16_t*>(logits), (long long)ld, reinterpret_cast<const long long*>(labels), lse,
+                      grad_scale, static_cast<uint16_t*>(dlogits), (long long)ldd, (int)V, (long long)ignore_index, (int)dtype));
+  return 0;
 }
 
 void lora_debug_set_phase_mask(int32_t mask) { g_phase_mask.store(mask & kPhaseAll, std::memory_order_relaxed); }

@@ -1,0 +1,160 @@
+"""The callers either side of the LoRA path, on the same kernels.
+
+* `FrozenLinear`: an un-adapted, frozen nn.Linear (in practice `lm_head`, which the reference leaves
+  untouched: target_modules at finetune_lora_distilgpt2.py:100 / finetune_lora_opt_pp.py:109 do not
+  name it) run through the tcgen05 GEMM of the LoRA path with the rank-r block off.  Its output may be
+  ragged (vocab 50257): it is written into a buffer whose row stride is padded to 8 elements and
+  returned as a strided view, so no copy and no mis-aligned library kernel.  Backward yields dX only.
+* `fused_causal_lm_loss`: mean next-token cross-entropy over labels != -100, computed from the 16-bit
+  logits in place of `logits.float()` + `F.cross_entropy` (DataCollatorForLanguageModeling semantics,
+  finetune_lora_distilgpt2.py:114; shifted CE of finetune_lora_opt_pp.py:143-153).  The shift is
+  applied to the labels, never to the logits.
+No CPU fallback: both raise on CPU tensors / fp32.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+import torch.nn as nn
+
+from . import binding
+
+
+def _p(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _pad8(n: int) -> int:
+    return (n + 7) // 8 * 8
+
+
+class _FrozenLinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, W, bias):
+        if not x.is_cuda:
+            raise RuntimeError("FrozenLinear needs CUDA tensors (no CPU fallback)")
+        K = x.shape[-1]
+        N = W.shape[0]
+        x2 = x.reshape(-1, K)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        M = x2.shape[0]
+        ldy = _pad8(N)
+        ybuf = torch.empty((M, ldy), dtype=x.dtype, device=x.device)
+        rc = binding.lib().lora_frozen_linear_fwd(_p(x2), K, _p(W), _p(bias), _p(ybuf), ldy, M, K, N,
+                                                  binding.dtype_code(x.dtype), 0, _stream())
+        binding._check(rc, "lora_frozen_linear_fwd")
+        ctx.save_for_backward(W)
+        ctx.meta = (x.shape, M, K, N)
+        return ybuf.view(*x.shape[:-1], ldy)[..., :N]  # strided view when N is ragged (row stride ldy)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (W,) = ctx.saved_tensors
+        x_shape, M, K, N = ctx.meta
+        if not ctx.needs_input_grad[0]:
+            return None, None, None
+        try:
+            dy2 = dy.view(M, N)  # keeps a padded-row layout (what the fused loss hands back) as it is
+        except RuntimeError:
+            dy2 = dy.reshape(M, N)
+        if dy2.stride(1) != 1 or dy2.stride(0) % 8 != 0 or dy2.data_ptr() % 16 != 0:
+            buf = torch.empty((M, _pad8(N)), dtype=dy.dtype, device=dy.device)
+            buf[:, :N].copy_(dy2)
+            dy2 = buf[:, :N]
+        dX = torch.empty((M, K), dtype=dy.dtype, device=dy.device)
+        rc = binding.lib().lora_frozen_linear_bwd(_p(dy2), dy2.stride(0), _p(W), _p(dX), K, M, K, N,
+                                                  binding.dtype_code(dy.dtype), 0, _stream())
+        binding._check(rc, "lora_frozen_linear_bwd")
+        return dX.view(x_shape), None, None
+
+
+class FrozenLinear(nn.Module):
+    """Wraps a frozen nn.Linear (shares its Parameters, so weight tying survives)."""
+
+    def __init__(self, base: nn.Linear):
+        super().__init__()
+        if not isinstance(base, nn.Linear):
+            raise ValueError("FrozenLinear wraps nn.Linear only")
+        if base.weight.requires_grad or (base.bias is not None and base.bias.requires_grad):
+            raise ValueError("FrozenLinear is for frozen layers: it produces no weight gradient")
+        self.base_layer = base
+        self.in_features, self.out_features = base.in_features, base.out_features
+
+    @property
+    def weight(self):
+        return self.base_layer.weight
+
+    @property
+    def bias(self):
+        return self.base_layer.bias
+
+    def forward(self, x):
+        W = self.base_layer.weight
+        if x.dtype != W.dtype:
+            x = x.to(W.dtype)
+        return _FrozenLinearFn.apply(x, W, self.base_layer.bias)
+
+
+def accelerate_lm_head(model: nn.Module) -> nn.Module:
+    """Swap `lm_head` (found on the model or below a PeftModel wrapper) for a FrozenLinear."""
+    for holder in (model, getattr(model, "base_model", None), getattr(getattr(model, "base_model", None), "model", None)):
+        if holder is None:
+            continue
+        head = holder.__dict__.get("_modules", {}).get("lm_head")
+        if isinstance(head, nn.Linear):
+            holder.lm_head = FrozenLinear(head)
+            return model
+    raise ValueError("no nn.Linear lm_head found")
+
+
+class _FusedCEFn(torch.autograd.Function):
+    """sum_i loss_i / n_valid over rows of a [M, V] 16-bit logits matrix (row stride % 8 == 0)."""
+
+    @staticmethod
+    def forward(ctx, logits2, labels1, ignore_index):
+        M, V = logits2.shape
+        ld = logits2.stride(0)
+        lse = torch.empty(M, dtype=torch.float32, device=logits2.device)
+        rows = torch.empty(M, dtype=torch.float32, device=logits2.device)
+        rc = binding.lib().lora_ce_fwd(_p(logits2), ld, _p(labels1), _p(lse), _p(rows), M, V, ignore_index,
+                                       binding.dtype_code(logits2.dtype), _stream())
+        binding._check(rc, "lora_ce_fwd")
+        n_valid = (labels1 != ignore_index).sum().clamp_min(1).to(torch.float32)
+        ctx.save_for_backward(logits2, labels1, lse, n_valid)
+        ctx.ignore_index = ignore_index
+        return rows.sum() / n_valid
+
+    @staticmethod
+    def backward(ctx, g):
+        logits2, labels1, lse, n_valid = ctx.saved_tensors
+        M, V = logits2.shape
+        ldd = _pad8(V)
+        dbuf = torch.empty((M, ldd), dtype=logits2.dtype, device=logits2.device)
+        scale = (g.to(torch.float32) / n_valid).reshape(1).contiguous()
+        rc = binding.lib().lora_ce_bwd(_p(logits2), logits2.stride(0), _p(labels1), _p(lse), _p(scale), _p(dbuf), ldd, M, V,
+                                       ctx.ignore_index, binding.dtype_code(logits2.dtype), _stream())
+        binding._check(rc, "lora_ce_bwd")
+        return dbuf[:, :V], None, None
+
+
+def fused_causal_lm_loss(logits: torch.Tensor, labels: torch.Tensor, ignore_index: int = -100) -> torch.Tensor:
+    """logits [B, S, V] (16-bit, CUDA; may be a padded-row view), labels [B, S] -> scalar fp32 loss."""
+    if not logits.is_cuda or logits.dtype not in (torch.bfloat16, torch.float16):
+        raise RuntimeError("fused_causal_lm_loss needs 16-bit CUDA logits (no CPU fallback)")
+    B, S, V = logits.shape
+    shifted = torch.full((B, S), ignore_index, dtype=torch.long, device=logits.device)
+    shifted[:, :-1] = labels[:, 1:]
+    if logits.stride(-1) == 1 and logits.stride(1) % 8 == 0 and logits.stride(0) == S * logits.stride(1) and \
+            logits.data_ptr() % 16 == 0:
+        l2 = logits.view(B * S, V)  # rows stay where they are (padded row stride allowed)
+    else:
+        buf = torch.empty((B * S, _pad8(V)), dtype=logits.dtype, device=logits.device)
+        buf[:, :V].copy_(logits.reshape(B * S, V))
+        l2 = buf[:, :V]
+    return _FusedCEFn.apply(l2, shifted.reshape(-1), int(ignore_index))

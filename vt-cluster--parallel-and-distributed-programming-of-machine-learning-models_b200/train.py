@@ -80,7 +80,9 @@ class Trainer:
     """Minimal stand-in for transformers.Trainer on this path (model(**batch) -> loss, backward,
     accumulate, reduce, clip, AdamW, linear decay)."""
 
-    def __init__(self, model: nn.Module, cfg: TrainConfig, on_step_end: Optional[Callable] = None):
+    def __init__(self, model: nn.Module, cfg: TrainConfig, on_step_end: Optional[Callable] = None,
+                 loss_fn: Optional[Callable] = None):
+        self.loss_fn = loss_fn or causal_lm_loss  # e.g. frozen.fused_causal_lm_loss on the GPU
         self.model = model
         self.cfg = cfg
         self.params = trainable_parameters(model)
@@ -106,7 +108,7 @@ class Trainer:
         with ctx:
             out = self.model(input_ids=batch["input_ids"], attention_mask=batch.get("attention_mask"))
             logits = out.logits if hasattr(out, "logits") else out
-            loss = causal_lm_loss(logits, batch["labels"]) / self.cfg.accum
+            loss = self.loss_fn(logits, batch["labels"]) / self.cfg.accum
             loss.backward()
         return loss.detach()
 
