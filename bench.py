@@ -382,6 +382,7 @@ def run_model(a, pkg, rank, world, device):
     loss_fn = None
     if not a.stock_head:
         pkg.frozen.accelerate_lm_head(pm)
+        pkg.frozen.accelerate_frozen_neighbours(pm)
         loss_fn = pkg.frozen.fused_causal_lm_loss
     net = pkg.train.wrap_ddp(pm, device) if world > 1 else pm
     tr = pkg.train.Trainer(net, pkg.train.TrainConfig(lr=5e-5, accum=1, total_steps=10 ** 6), loss_fn=loss_fn)

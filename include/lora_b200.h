@@ -148,6 +148,25 @@ int lora_frozen_linear_bwd(const void* dY, int64_t lddy, const void* W, void* dX
                            int64_t N, int32_t dtype, int32_t w_is_KN, cudaStream_t stream);
 
 /*
+ * Frozen projection with its activation applied in the GEMM epilogue: the
+ * un-adapted `mlp.c_fc` + gelu_new of GPT-2 blocks (c_fc is no LoRA target at
+ * finetune_lora_distilgpt2.py:100; HF runs addmm followed by ~8 elementwise kernels of
+ * NewGELUActivation) and, when fc1 is not targeted (BASELINE configs[3], q_proj/v_proj), OPT's
+ * fc1 + relu.  Y = act(X W^T + bias) with act = LORA_ACT_RELU | LORA_ACT_GELU_NEW; Z (optional,
+ * may be NULL) receives the pre-activation X W^T + bias, which gelu_new's backward needs.
+ * lora_act_bwd: dZ = dY * act'(.) elementwise over n_elems (multiple of 8) contiguous elements;
+ * the second operand is Z for gelu_new and Y (or Z) for relu.  dX then comes from
+ * lora_frozen_linear_bwd(dZ, ...).
+ */
+#define LORA_ACT_RELU 1
+#define LORA_ACT_GELU_NEW 2
+int lora_frozen_linear_act_fwd(const void* X, int64_t ldx, const void* W, const void* bias, void* Y, int64_t ldy, void* Z,
+                               int64_t ldz, int64_t M, int64_t K, int64_t N, int32_t act, int32_t dtype, int32_t w_is_KN,
+                               cudaStream_t stream);
+int lora_act_bwd(const void* dY, const void* ZorY, void* dZ, int64_t n_elems, int32_t act, int32_t dtype,
+                 cudaStream_t stream);
+
+/*
  * Token cross-entropy from 16-bit logits; replaces the fp32 logits copy +
  * log_softmax + nll_loss that the HF causal-LM loss runs on DataCollatorForLanguageModeling labels
  * (finetune_lora_distilgpt2.py:114) and nn.CrossEntropyLoss in finetune_lora_opt_pp.py:143-153.

@@ -59,6 +59,78 @@ def test_fused_causal_lm_loss_matches_oracle(pkg, B, S, V, dtype):
     assert float(lg.grad[0, 2:5].float().abs().max()) == 0.0  # rows whose shifted label is -100
 
 
+@pytest.mark.parametrize("M,K,N,act,conv1d,dtype", [
+    (300, 256, 1024, "gelu_new", True, torch.bfloat16),
+    (4096, 768, 3072, "gelu_new", True, torch.bfloat16),
+    (520, 512, 2048, "relu", False, torch.float16),
+    (130, 256, 264, "relu", False, torch.bfloat16),
+    (130, 256, 264, None, True, torch.bfloat16),
+])
+def test_frozen_linear_activation_epilogue(pkg, M, K, N, act, conv1d, dtype):
+    """Frozen c_fc + gelu_new (GPT-2 Conv1D layout) / fc1 + relu against the fp32 torch formula."""
+    from transformers.activations import NewGELUActivation
+    from transformers.pytorch_utils import Conv1D
+
+    g = torch.Generator().manual_seed(4)
+    x = torch.randn(M, K, generator=g).to(dtype)
+    W = (torch.randn(N, K, generator=g) * 0.05).to(dtype)
+    b = (torch.randn(N, generator=g) * 0.1).to(dtype)
+    dy = torch.randn(M, N, generator=g).to(dtype)
+    if conv1d:
+        base = Conv1D(N, K)
+        with torch.no_grad():
+            base.weight.copy_(W.t().float())
+            base.bias.copy_(b.float())
+    else:
+        base = torch.nn.Linear(K, N)
+        with torch.no_grad():
+            base.weight.copy_(W.float())
+            base.bias.copy_(b.float())
+    base = base.to(dtype).requires_grad_(False).cuda()
+    fl = pkg.frozen.FrozenLinear(base, act=act)
+    xg = x.cuda().requires_grad_(True)
+    y = fl(xg)
+    y.backward(dy.cuda())
+    xr = x.float().requires_grad_(True)
+    z = xr @ W.float().t() + b.float()
+    ref = {"gelu_new": NewGELUActivation(), "relu": torch.nn.ReLU(), None: torch.nn.Identity()}[act](z)
+    ref.backward(dy.float())
+    assert relerr(y, ref) < TOL and relerr(xg.grad, xr.grad) < TOL
+    with torch.no_grad():  # inference path: no pre-activation buffer
+        assert relerr(fl(x.cuda()), ref) < TOL
+
+
+def test_opt_layer_with_frozen_neighbours_matches_stock_path(pkg):
+    from transformers import OPTConfig, OPTForCausalLM
+
+    torch.manual_seed(0)
+    base = OPTForCausalLM(OPTConfig(num_hidden_layers=2, hidden_size=256, ffn_dim=1024, num_attention_heads=4,
+                                    vocab_size=1000, word_embed_proj_dim=256, max_position_embeddings=64,
+                                    dropout=0.0)).to(torch.bfloat16)
+    cfg = pkg.LoraConfig(r=8, lora_alpha=16, target_modules=["q_proj", "v_proj"], task_type=pkg.TaskType.CAUSAL_LM)
+    ids = torch.randint(2, 1000, (2, 48), generator=torch.Generator().manual_seed(2)).cuda()
+    res = []
+    for fast in (False, True):
+        torch.manual_seed(5)
+        pm = pkg.get_peft_model(copy.deepcopy(base), cfg).cuda()
+        with torch.no_grad():
+            for n, p in pm.named_parameters():
+                if "lora_B" in n:
+                    p.copy_(torch.randn(p.shape, generator=torch.Generator().manual_seed(3)).to(p.device) * 0.02)
+        if fast:
+            assert pkg.frozen.accelerate_frozen_neighbours(pm, plain=True) == 2 * 4
+            pkg.frozen.accelerate_lm_head(pm)
+        pm.train()
+        logits = pm(input_ids=ids).logits
+        loss = pkg.frozen.fused_causal_lm_loss(logits, ids) if fast else pkg.train.causal_lm_loss(logits, ids)
+        loss.backward()
+        res.append((float(loss), {n: p.grad.clone() for n, p in pm.named_parameters() if p.requires_grad}))
+    assert abs(res[0][0] - res[1][0]) / res[0][0] < 5e-3
+    for n in res[0][1]:
+        a, b = res[1][1][n].float().flatten(), res[0][1][n].float().flatten()
+        assert float(torch.nn.functional.cosine_similarity(a, b, dim=0)) > 0.98, n  # bf16 + relu: see test_gpu_model
+
+
 def test_model_with_fast_head_and_loss_matches_stock_path(pkg):
     """distilgpt2-style model with a ragged vocab: swapping lm_head + loss changes nothing but speed."""
     from transformers import GPT2Config, GPT2LMHeadModel
@@ -79,6 +151,7 @@ def test_model_with_fast_head_and_loss_matches_stock_path(pkg):
         if fast:
             pkg.frozen.accelerate_lm_head(pm)
             assert isinstance(pm.base_model.model.lm_head, pkg.frozen.FrozenLinear)
+            assert pkg.frozen.accelerate_frozen_neighbours(pm) == 2  # c_fc + gelu_new of both blocks
         pm.train()
         logits = pm(input_ids=ids).logits
         loss = pkg.frozen.fused_causal_lm_loss(logits, ids) if fast else pkg.train.causal_lm_loss(logits, ids)

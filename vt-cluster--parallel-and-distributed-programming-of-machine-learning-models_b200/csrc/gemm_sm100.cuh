@@ -66,7 +66,30 @@ struct Params {
   const void* a16_rows; // A as [dh_ld, N] dtype (column index contiguous), padding rows zero
   const uint8_t* keep;  // [M, N/8] keep bits
   float inv_keep;
+  // activation epilogue (kAct instantiation, un-adapted neighbours of the LoRA path): D = act(acc + bias)
+  int act;      // kActNone / kActRelu / kActGeluNew
+  int store_z;  // also store the pre-activation acc + bias through tmZ (gelu_new backward needs it)
 };
+
+constexpr int kActNone = 0, kActRelu = 1, kActGeluNew = 2;
+
+// gelu_new of HF GPT-2 (transformers NewGELUActivation): 0.5 x (1 + tanh(sqrt(2/pi) (x + 0.044715 x^3))).
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float gelu_new(float x) {
+  const float u = 0.7978845608028654f * fmaf(0.044715f * x * x, x, x);
+  return 0.5f * x * (1.f + tanh_approx(u));
+}
+__device__ __forceinline__ float gelu_new_grad(float x) {
+  const float x2 = x * x;
+  const float u = 0.7978845608028654f * fmaf(0.044715f * x2, x, x);
+  const float t = tanh_approx(u);
+  const float du = 0.7978845608028654f * fmaf(3.f * 0.044715f, x2, 1.f);
+  return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * du;
+}
 
 __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int& m_blk, int& n_blk) {
   const int group_sz = GROUP_M * num_n;
@@ -113,11 +136,14 @@ __device__ __forceinline__ void cluster_sync_all() {
 
 // kMasked: backward with dropout -- the rank-r term keep/(1-p) .* (dH A) is formed in the
 // epilogue (warp-level MMA + keep-bits) instead of riding the main loop as a K-block.
-template <bool kMasked, bool kPair>
+// kAct (unmasked only): the epilogue applies relu / gelu_new after the bias and can store the
+// pre-activation as a second output (tmZ); used for the frozen, un-adapted layers next to the path.
+template <bool kMasked, bool kPair, bool kAct = false>
 __global__ void __launch_bounds__(THREADS, 1)
     gemm_lora_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                      const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
-                     const __grid_constant__ CUtensorMap tmD, const Params p) {
+                     const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmZ, const Params p) {
+  static_assert(!(kMasked && kAct), "the activation epilogue belongs to the unmasked kernel");
   using C = Cfg<kPair, kMasked>;
   constexpr int STAGES = C::STAGES;
   constexpr int STAGE_BYTES = C::STAGE_BYTES;
@@ -392,7 +418,77 @@ __global__ void __launch_bounds__(THREADS, 1)
       tc_fence_after();
 
       const bool warp_rows_ok = rbase < p.M;  // else this warp's 32 rows are all padding
-      if constexpr (!kMasked) {
+      if constexpr (kAct) {
+        // Activation epilogue: each 64-column group is staged twice (pre-activation in buffer 0 when
+        // asked for, activation in buffer 1) and leaves through two TMA stores.
+        if (warp_rows_ok) {
+          const int nchunks = (min(BN, p.N - n_blk * BN) + 31) / 32;  // warp-uniform, >= 1
+          const uint32_t tbase = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + buf * BN;
+          uint32_t v[32];
+          for (int ci = 0; ci < nchunks; ci += 2) {
+            const int col0 = n_blk * BN + ci * 32;
+            if (lane == 0) bulk_wait_group_read<0>();  // both staging buffers are rewritten below
+            __syncwarp();
+            uint8_t* zdst = my_stage + lane * 128;
+            uint8_t* ydst = my_stage + EPI_BUF_BYTES + lane * 128;
+            for (int h = 0; h < 2 && ci + h < nchunks; ++h) {
+              tmem_ld_32x32b_x32(tbase + (ci + h) * 32, v);
+              tmem_ld_wait();
+              const int c = col0 + h * 32;
+              if (p.bias != nullptr) {
+                const uint4* bp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.bias) + c);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  if (c + q * 8 < p.N) {
+                    const uint4 bw = load_bias8(bp + q, p.N - (c + q * 8));
+                    const uint32_t w4[4] = {bw.x, bw.y, bw.z, bw.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                      const float2 f = unpack2(w4[e], dtype);
+                      v[q * 8 + e * 2] = __float_as_uint(__uint_as_float(v[q * 8 + e * 2]) + f.x);
+                      v[q * 8 + e * 2 + 1] = __float_as_uint(__uint_as_float(v[q * 8 + e * 2 + 1]) + f.y);
+                    }
+                  }
+                }
+              }
+              if (p.store_z) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  uint4 o;
+                  o.x = pack2(__uint_as_float(v[q * 8 + 0]), __uint_as_float(v[q * 8 + 1]), dtype);
+                  o.y = pack2(__uint_as_float(v[q * 8 + 2]), __uint_as_float(v[q * 8 + 3]), dtype);
+                  o.z = pack2(__uint_as_float(v[q * 8 + 4]), __uint_as_float(v[q * 8 + 5]), dtype);
+                  o.w = pack2(__uint_as_float(v[q * 8 + 6]), __uint_as_float(v[q * 8 + 7]), dtype);
+                  *reinterpret_cast<uint4*>(zdst + (((h * 4 + q) ^ (lane & 7)) << 4)) = o;
+                }
+              }
+              if (p.act == kActGeluNew) {
+#pragma unroll
+                for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(gelu_new(__uint_as_float(v[e])));
+              } else if (p.act == kActRelu) {
+#pragma unroll
+                for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(fmaxf(__uint_as_float(v[e]), 0.f));
+              }
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                uint4 o;
+                o.x = pack2(__uint_as_float(v[q * 8 + 0]), __uint_as_float(v[q * 8 + 1]), dtype);
+                o.y = pack2(__uint_as_float(v[q * 8 + 2]), __uint_as_float(v[q * 8 + 3]), dtype);
+                o.z = pack2(__uint_as_float(v[q * 8 + 4]), __uint_as_float(v[q * 8 + 5]), dtype);
+                o.w = pack2(__uint_as_float(v[q * 8 + 6]), __uint_as_float(v[q * 8 + 7]), dtype);
+                *reinterpret_cast<uint4*>(ydst + (((h * 4 + q) ^ (lane & 7)) << 4)) = o;
+              }
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              if (p.store_z) tma_store_2d(&tmZ, my_stage, col0, rbase);
+              tma_store_2d(&tmD, my_stage + EPI_BUF_BYTES, col0, rbase);
+              bulk_commit_group();
+            }
+          }
+        }
+      } else if constexpr (!kMasked) {
         // Plain epilogue, software-pipelined: the TMEM load of the next 32-column chunk is in flight
         // while the current one is biased, converted and staged (two register sets alternate).
         if (warp_rows_ok) {

@@ -12,6 +12,7 @@
 #include <string>
 #include <utility>
 
+#include "act.cuh"
 #include "ce.cuh"
 #include "gemm_sm100.cuh"
 #include "lora_b200.h"
@@ -136,6 +137,8 @@ int device_setup(int* sm_count) {
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<true, false>, gemm::SMEM_BYTES));
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false, true>, gemm::SMEM_BYTES));
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<true, true>, gemm::SMEM_BYTES));
+    CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false, false, true>, gemm::SMEM_BYTES));
+    CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false, true, true>, gemm::SMEM_BYTES));
 #define OPT_IN_SKINNY(BF, RP)                                                                     \
   CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP>, skinny::rp_smem_bytes<RP>()));             \
   CUDA_TRY(opt_in_smem(skinny::colproj_kernel<BF, RP>, skinny::cp_smem_bytes<RP>()));
@@ -347,6 +350,9 @@ struct GemmArgs {
   const void* a16_rows;
   const uint8_t* keep;
   float inv_keep;
+  int act = 0;          // gemm::kActRelu / kActGeluNew: activation epilogue (frozen neighbours only)
+  void* Z = nullptr;    // pre-activation output [M, N] (optional, act != 0)
+  int64_t ldz = 0;
 };
 
 // LORA_B200_GEMM=1cta forces the single-CTA tile shape (A/B testing); default: CTA pairs whenever
@@ -359,18 +365,18 @@ bool pair_mode_allowed() {
   return allowed;
 }
 
-template <bool kMasked, bool kPair>
+template <bool kMasked, bool kPair, bool kAct = false>
 int launch_gemm_t(const CUtensorMap& tmA1, const CUtensorMap& tmB1, const CUtensorMap& tmA2, const CUtensorMap& tmB2,
-                  const CUtensorMap& tmD, const gemm::Params& p, int grid, cudaStream_t stream) {
-  CUDA_TRY(launch_pdl(gemm::gemm_lora_kernel<kMasked, kPair>, dim3(grid), dim3(gemm::THREADS), gemm::SMEM_BYTES, stream,
-                      kPair ? 2 : 1, tmA1, tmB1, tmA2, tmB2, tmD, p));
+                  const CUtensorMap& tmD, const CUtensorMap& tmZ, const gemm::Params& p, int grid, cudaStream_t stream) {
+  CUDA_TRY(launch_pdl(gemm::gemm_lora_kernel<kMasked, kPair, kAct>, dim3(grid), dim3(gemm::THREADS), gemm::SMEM_BYTES,
+                      stream, kPair ? 2 : 1, tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p));
   return 0;
 }
 
 int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, int sm_count, cudaStream_t stream) {
   const bool pair = pair_mode_allowed() && M > gemm::BM && sm_count >= 2;
   const uint32_t b_rows = pair ? gemm::BN / 2 : gemm::BN;  // rows of the B tile one CTA stages
-  CUtensorMap tmA1, tmB1, tmA2, tmB2, tmD;
+  CUtensorMap tmA1, tmB1, tmA2, tmB2, tmD, tmZ;
   if (make_tmap(&tmA1, g.A1, dtype, K1, M, g.lda1 ? g.lda1 : K1, gemm::BK, gemm::BM, CU_TENSOR_MAP_SWIZZLE_128B, "gemm A1")) return 1;
   if (!g.b_mn_major) {
     if (make_tmap(&tmB1, g.B1, dtype, K1, N, K1, gemm::BK, b_rows, CU_TENSOR_MAP_SWIZZLE_128B, "gemm B1 (K-major)")) return 1;
@@ -386,6 +392,8 @@ int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, 
     tmB2 = tmB1;
   }
   if (make_tmap(&tmD, g.D, dtype, N, M, g.ldd ? g.ldd : N, 64, 32, CU_TENSOR_MAP_SWIZZLE_128B, "gemm D")) return 1;
+  tmZ = tmD;
+  if (g.Z && make_tmap(&tmZ, g.Z, dtype, N, M, g.ldz ? g.ldz : N, 64, 32, CU_TENSOR_MAP_SWIZZLE_128B, "gemm Z")) return 1;
 
   gemm::Params p;
   p.M = (int)M;
@@ -402,18 +410,23 @@ int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, 
   p.a16_rows = g.a16_rows;
   p.keep = g.keep;
   p.inv_keep = g.inv_keep;
+  p.act = g.act;
+  p.store_z = g.Z != nullptr;
 
   const int tile_m = pair ? 2 * gemm::BM : gemm::BM;
   const long long tiles = ((M + tile_m - 1) / tile_m) * ((N + gemm::BN - 1) / gemm::BN);
   const bool masked = p.masked_r > 0;
+  if (masked && p.act) return fail("internal: activation epilogue with the masked kernel");
   if (pair) {
     const int grid = 2 * static_cast<int>(std::min<long long>(tiles, sm_count / 2));
-    return masked ? launch_gemm_t<true, true>(tmA1, tmB1, tmA2, tmB2, tmD, p, grid, stream)
-                  : launch_gemm_t<false, true>(tmA1, tmB1, tmA2, tmB2, tmD, p, grid, stream);
+    if (p.act) return launch_gemm_t<false, true, true>(tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p, grid, stream);
+    return masked ? launch_gemm_t<true, true>(tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p, grid, stream)
+                  : launch_gemm_t<false, true>(tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p, grid, stream);
   }
   const int grid = static_cast<int>(std::min<long long>(tiles, sm_count));
-  return masked ? launch_gemm_t<true, false>(tmA1, tmB1, tmA2, tmB2, tmD, p, grid, stream)
-                : launch_gemm_t<false, false>(tmA1, tmB1, tmA2, tmB2, tmD, p, grid, stream);
+  if (p.act) return launch_gemm_t<false, false, true>(tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p, grid, stream);
+  return masked ? launch_gemm_t<true, false>(tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p, grid, stream)
+                : launch_gemm_t<false, false>(tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p, grid, stream);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -624,6 +637,51 @@ int lora_frozen_linear_fwd(const void* X, int64_t ldx, const void* W, const void
   g.bias = bias;
   g.inv_keep = 1.f;
   return launch_gemm(g, M, N, K, dtype, sms, stream);
+}
+
+int lora_frozen_linear_act_fwd(const void* X, int64_t ldx, const void* W, const void* bias, void* Y, int64_t ldy, void* Z,
+                               int64_t ldz, int64_t M, int64_t K, int64_t N, int32_t act, int32_t dtype, int32_t w_is_KN,
+                               cudaStream_t stream) {
+  g_err.clear();
+  if (M <= 0 || K <= 0 || N <= 0 || M > INT32_MAX || K > INT32_MAX || N > INT32_MAX) return fail("lora_frozen_linear_act_fwd: bad shape");
+  if (dtype != kDtypeBf16 && dtype != kDtypeFp16) return fail("dtype must be 0 (bf16) or 1 (fp16); fp32 is not supported");
+  if (!X || !W || !Y) return fail("lora_frozen_linear_act_fwd: null pointer argument");
+  if (act != gemm::kActRelu && act != gemm::kActGeluNew) return fail("lora_frozen_linear_act_fwd: act must be 1 (relu) or 2 (gelu_new); got %d", act);
+  if (ldx < K || ldy < N || ldx % 8 || ldy % 8 || (Z && (ldz < N || ldz % 8)))
+    return fail("lora_frozen_linear_act_fwd: ldx/ldy/ldz must be >= K/N/N and multiples of 8 elements");
+  if ((w_is_KN ? N : K) % 8) return fail("lora_frozen_linear_act_fwd: the weight's row length (%s) must be a multiple of 8", w_is_KN ? "N" : "K");
+  int sms = 0;
+  if (device_setup(&sms)) return 1;
+  GemmArgs g{};
+  g.A1 = X;
+  g.lda1 = ldx;
+  g.B1 = W;
+  g.b_mn_major = w_is_KN ? 1 : 0;
+  g.D = Y;
+  g.ldd = ldy;
+  g.bias = bias;
+  g.inv_keep = 1.f;
+  g.act = act;
+  g.Z = Z;
+  g.ldz = ldz;
+  return launch_gemm(g, M, N, K, dtype, sms, stream);
+}
+
+int lora_act_bwd(const void* dY, const void* ZorY, void* dZ, int64_t n_elems, int32_t act, int32_t dtype, cudaStream_t stream) {
+  g_err.clear();
+  if (!dY || !ZorY || !dZ) return fail("lora_act_bwd: null pointer argument");
+  if (n_elems <= 0 || n_elems % 8) return fail("lora_act_bwd: element count must be a positive multiple of 8");
+  if (act != gemm::kActRelu && act != gemm::kActGeluNew) return fail("lora_act_bwd: act must be 1 (relu) or 2 (gelu_new); got %d", act);
+  if (dtype != kDtypeBf16 && dtype != kDtypeFp16) return fail("dtype must be 0 (bf16) or 1 (fp16); fp32 is not supported");
+  if ((reinterpret_cast<uintptr_t>(dY) | reinterpret_cast<uintptr_t>(ZorY) | reinterpret_cast<uintptr_t>(dZ)) & 15)
+    return fail("lora_act_bwd: pointers must be 16-byte aligned");
+  int sms = 0;
+  if (device_setup(&sms)) return 1;
+  const long long n8 = n_elems / 8;
+  const int grid = static_cast<int>(std::min<long long>((n8 + act::THREADS - 1) / act::THREADS, 8LL * sms));
+  CUDA_TRY(launch_pdl(act::act_bwd_kernel, dim3(grid), dim3(act::THREADS), 0, stream, 1, static_cast<const uint4*>(dY),
+                      static_cast<const uint4*>(ZorY), static_cast<uint4*>(dZ), n8, (int)act, (int)dtype));
+  return 0;
 }
 
 int lora_frozen_linear_bwd(const void* dY, int64_t lddy, const void* W, void* dX, int64_t lddx, int64_t M, int64_t K,

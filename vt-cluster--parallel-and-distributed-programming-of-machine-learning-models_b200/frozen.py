@@ -1,5 +1,9 @@
 """The callers either side of the LoRA path, on the same kernels.
 
+* `FrozenLinear(base, act=...)` with an activation: the frozen `mlp.c_fc` + gelu_new of a GPT-2 block
+  (c_fc is not a LoRA target, finetune_lora_distilgpt2.py:100) or OPT's fc1 + relu when fc1 is not
+  targeted (BASELINE configs[3]); the activation runs in the GEMM epilogue, its backward is one
+  elementwise kernel.  `accelerate_frozen_neighbours(model)` does the module surgery.
 * `FrozenLinear`: an un-adapted, frozen nn.Linear (in practice `lm_head`, which the reference leaves
   untouched: target_modules at finetune_lora_distilgpt2.py:100 / finetune_lora_opt_pp.py:109 do not
   name it) run through the tcgen05 GEMM of the LoRA path with the rank-r block off.  Its output may be
@@ -35,11 +39,11 @@ def _pad8(n: int) -> int:
 
 class _FrozenLinearFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, W, bias):
+    def forward(ctx, x, W, bias, w_is_KN=0):
         if not x.is_cuda:
             raise RuntimeError("FrozenLinear needs CUDA tensors (no CPU fallback)")
         K = x.shape[-1]
-        N = W.shape[0]
+        N = W.shape[1] if w_is_KN else W.shape[0]
         x2 = x.reshape(-1, K)
         if not x2.is_contiguous():
             x2 = x2.contiguous()
@@ -47,18 +51,18 @@ class _FrozenLinearFn(torch.autograd.Function):
         ldy = _pad8(N)
         ybuf = torch.empty((M, ldy), dtype=x.dtype, device=x.device)
         rc = binding.lib().lora_frozen_linear_fwd(_p(x2), K, _p(W), _p(bias), _p(ybuf), ldy, M, K, N,
-                                                  binding.dtype_code(x.dtype), 0, _stream())
+                                                  binding.dtype_code(x.dtype), w_is_KN, _stream())
         binding._check(rc, "lora_frozen_linear_fwd")
         ctx.save_for_backward(W)
-        ctx.meta = (x.shape, M, K, N)
+        ctx.meta = (x.shape, M, K, N, w_is_KN)
         return ybuf.view(*x.shape[:-1], ldy)[..., :N]  # strided view when N is ragged (row stride ldy)
 
     @staticmethod
     def backward(ctx, dy):
         (W,) = ctx.saved_tensors
-        x_shape, M, K, N = ctx.meta
+        x_shape, M, K, N, w_is_KN = ctx.meta
         if not ctx.needs_input_grad[0]:
-            return None, None, None
+            return None, None, None, None
         try:
             dy2 = dy.view(M, N)  # keeps a padded-row layout (what the fused loss hands back) as it is
         except RuntimeError:
@@ -69,22 +73,80 @@ class _FrozenLinearFn(torch.autograd.Function):
             dy2 = buf[:, :N]
         dX = torch.empty((M, K), dtype=dy.dtype, device=dy.device)
         rc = binding.lib().lora_frozen_linear_bwd(_p(dy2), dy2.stride(0), _p(W), _p(dX), K, M, K, N,
-                                                  binding.dtype_code(dy.dtype), 0, _stream())
+                                                  binding.dtype_code(dy.dtype), w_is_KN, _stream())
         binding._check(rc, "lora_frozen_linear_bwd")
-        return dX.view(x_shape), None, None
+        return dX.view(x_shape), None, None, None
+
+
+ACT_CODES = {None: 0, "relu": 1, "gelu_new": 2}
+
+
+def _weight_layout(base):
+    """(in_features, out_features, w_is_KN) of nn.Linear ([N,K]) or HF Conv1D ([K,N])."""
+    if isinstance(base, nn.Linear):
+        return base.in_features, base.out_features, 0
+    if type(base).__name__ == "Conv1D" and hasattr(base, "nf"):
+        return base.weight.shape[0], base.weight.shape[1], 1
+    raise ValueError(f"FrozenLinear wraps nn.Linear or transformers Conv1D, not {type(base).__name__}")
+
+
+class _FrozenActLinearFn(torch.autograd.Function):
+    """y = act(x W^T + b) for a frozen W; saves the pre-activation (gelu_new) or y (relu) for dX."""
+
+    @staticmethod
+    def forward(ctx, x, W, bias, act, w_is_KN):
+        if not x.is_cuda:
+            raise RuntimeError("FrozenLinear needs CUDA tensors (no CPU fallback)")
+        K = x.shape[-1]
+        N = W.shape[1] if w_is_KN else W.shape[0]
+        if N % 8:
+            raise RuntimeError("FrozenLinear with an activation needs out_features % 8 == 0")
+        x2 = x.reshape(-1, K)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        M = x2.shape[0]
+        need_grad = any(ctx.needs_input_grad)
+        y = torch.empty((M, N), dtype=x.dtype, device=x.device)
+        z = torch.empty((M, N), dtype=x.dtype, device=x.device) if (need_grad and act == 2) else None
+        rc = binding.lib().lora_frozen_linear_act_fwd(_p(x2), K, _p(W), _p(bias), _p(y), N, _p(z), N, M, K, N, act,
+                                                      binding.dtype_code(x.dtype), w_is_KN, _stream())
+        binding._check(rc, "lora_frozen_linear_act_fwd")
+        ctx.save_for_backward(W, z if act == 2 else y)
+        ctx.meta = (x.shape, M, K, N, act, w_is_KN)
+        return y.view(*x.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        W, saved = ctx.saved_tensors
+        x_shape, M, K, N, act, w_is_KN = ctx.meta
+        if not ctx.needs_input_grad[0]:
+            return None, None, None, None, None
+        dy2 = dy.reshape(M, N)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        code = binding.dtype_code(dy.dtype)
+        dz = torch.empty((M, N), dtype=dy.dtype, device=dy.device)
+        rc = binding.lib().lora_act_bwd(_p(dy2), _p(saved), _p(dz), M * N, act, code, _stream())
+        binding._check(rc, "lora_act_bwd")
+        dX = torch.empty((M, K), dtype=dy.dtype, device=dy.device)
+        rc = binding.lib().lora_frozen_linear_bwd(_p(dz), N, _p(W), _p(dX), K, M, K, N, code, w_is_KN, _stream())
+        binding._check(rc, "lora_frozen_linear_bwd")
+        return dX.view(x_shape), None, None, None, None
 
 
 class FrozenLinear(nn.Module):
-    """Wraps a frozen nn.Linear (shares its Parameters, so weight tying survives)."""
+    """Wraps a frozen nn.Linear or HF Conv1D (shares its Parameters, so weight tying survives);
+    `act` in (None, "relu", "gelu_new") is applied in the GEMM epilogue."""
 
-    def __init__(self, base: nn.Linear):
+    def __init__(self, base: nn.Module, act=None):
         super().__init__()
-        if not isinstance(base, nn.Linear):
-            raise ValueError("FrozenLinear wraps nn.Linear only")
+        self.in_features, self.out_features, self.w_is_KN = _weight_layout(base)
         if base.weight.requires_grad or (base.bias is not None and base.bias.requires_grad):
             raise ValueError("FrozenLinear is for frozen layers: it produces no weight gradient")
+        if act not in ACT_CODES:
+            raise ValueError(f"act must be one of {list(ACT_CODES)}")
         self.base_layer = base
-        self.in_features, self.out_features = base.in_features, base.out_features
+        self.act = act
 
     @property
     def weight(self):
@@ -98,7 +160,46 @@ class FrozenLinear(nn.Module):
         W = self.base_layer.weight
         if x.dtype != W.dtype:
             x = x.to(W.dtype)
-        return _FrozenLinearFn.apply(x, W, self.base_layer.bias)
+        if self.act is None:
+            return _FrozenLinearFn.apply(x, W, self.base_layer.bias, self.w_is_KN)
+        return _FrozenActLinearFn.apply(x, W, self.base_layer.bias, ACT_CODES[self.act], self.w_is_KN)
+
+    def extra_repr(self):
+        return f"in_features={self.in_features}, out_features={self.out_features}, act={self.act}"
+
+
+def _is_frozen_plain(m):
+    try:
+        _weight_layout(m)
+    except ValueError:
+        return False
+    return not m.weight.requires_grad and (m.bias is None or not m.bias.requires_grad)
+
+
+def accelerate_frozen_neighbours(model: nn.Module, plain: bool = False) -> int:
+    """Module surgery on the un-adapted neighbours of the LoRA path; returns how many layers changed.
+    GPT-2 blocks: frozen `mlp.c_fc` followed by NewGELUActivation -> one GEMM with gelu_new epilogue.
+    OPT layers: frozen `fc1` followed by ReLU -> one GEMM with relu epilogue.
+    plain=True also moves every other frozen nn.Linear / Conv1D inside those blocks onto the kernel."""
+    n = 0
+    for mod in list(model.modules()):
+        kids = mod._modules
+        if "c_fc" in kids and "act" in kids and _is_frozen_plain(kids["c_fc"]) and \
+                type(kids["act"]).__name__ == "NewGELUActivation":
+            mod.c_fc = FrozenLinear(kids["c_fc"], act="gelu_new")
+            mod.act = nn.Identity()
+            n += 1
+        if "fc1" in kids and "activation_fn" in kids and _is_frozen_plain(kids["fc1"]) and \
+                isinstance(kids["activation_fn"], nn.ReLU):
+            mod.fc1 = FrozenLinear(kids["fc1"], act="relu")
+            mod.activation_fn = nn.Identity()
+            n += 1
+        if plain and type(mod).__name__ in ("GPT2MLP", "GPT2Attention", "OPTAttention", "OPTDecoderLayer"):
+            for name, kid in list(kids.items()):
+                if _is_frozen_plain(kid) and kid.weight.shape[0] % 8 == 0 and kid.weight.shape[1] % 8 == 0:
+                    setattr(mod, name, FrozenLinear(kid))
+                    n += 1
+    return n
 
 
 def accelerate_lm_head(model: nn.Module) -> nn.Module:
