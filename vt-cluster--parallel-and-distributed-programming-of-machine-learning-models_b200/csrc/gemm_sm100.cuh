@@ -47,7 +47,8 @@ constexpr int EPI_WARPS = 4;
 constexpr int EPI_BUF_BYTES = 32 * 128;  // 32 rows x 64 cols x 2 B
 constexpr int EPI_BYTES = EPI_WARPS * 2 * EPI_BUF_BYTES;
 constexpr int BAR_BYTES = 256;
-constexpr int SMEM_BYTES = 4 * (A_TILE_BYTES + BN * BK * 2) + EPI_BYTES + BAR_BYTES + 1024;  // same for both
+constexpr int BIAS_BYTES = BN * 4;  // the tile's bias slice as fp32 (unmasked kernels)
+constexpr int SMEM_BYTES = 4 * (A_TILE_BYTES + BN * BK * 2) + EPI_BYTES + BAR_BYTES + BIAS_BYTES + 1024;  // same for both
 constexpr int THREADS = 256;
 constexpr int TMEM_COLS = 512;
 constexpr int GROUP_M = 16;  // m-blocks (of one CTA or one pair) per raster group (L2 reuse of B panels)
@@ -159,6 +160,7 @@ __global__ void __launch_bounds__(THREADS, 1)
   uint64_t* tmem_full = bars + 2 * STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  float* bias_s = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + BAR_BYTES);  // [BN]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -414,78 +416,98 @@ __global__ void __launch_bounds__(THREADS, 1)
           }
       }
 
+      if constexpr (!kMasked) {
+        // The tile's 256 bias values go to smem (fp32) while the main loop is still running: with
+        // ~225 KiB of the SM's 256 KiB configured as shared memory there is no L1 to speak of, and a
+        // per-chunk __ldg would stall every chunk for an L2 round trip.
+        if (p.bias != nullptr) {
+          asm volatile("bar.sync 2, 128;" ::: "memory");  // every warp is done with the previous tile's slice
+          const int t128 = ew * 32 + lane;
+          const int col = n_blk * BN + 2 * t128;
+          const uint16_t* bp = reinterpret_cast<const uint16_t*>(p.bias) + col;
+          uint32_t w = 0u;
+          if (col + 1 < p.N) w = __ldg(reinterpret_cast<const uint32_t*>(bp));
+          else if (col < p.N) w = __ldg(bp);
+          const float2 f = unpack2(w, dtype);
+          *reinterpret_cast<float2*>(bias_s + 2 * t128) = f;
+          asm volatile("bar.sync 2, 128;" ::: "memory");
+        }
+      }
+
       mbar_wait(&tmem_full[buf], acc_phase, 4);
       tc_fence_after();
 
       const bool warp_rows_ok = rbase < p.M;  // else this warp's 32 rows are all padding
       if constexpr (kAct) {
-        // Activation epilogue: each 64-column group is staged twice (pre-activation in buffer 0 when
-        // asked for, activation in buffer 1) and leaves through two TMA stores.
+        // Activation epilogue, software-pipelined like the plain one.  With the pre-activation asked
+        // for, each 64-column group is staged twice (Z in buffer 0, act(Z) in buffer 1) and leaves
+        // through two TMA stores; without it the two buffers alternate.
         if (warp_rows_ok) {
           const int nchunks = (min(BN, p.N - n_blk * BN) + 31) / 32;  // warp-uniform, >= 1
           const uint32_t tbase = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + buf * BN;
-          uint32_t v[32];
+          const bool store_z = p.store_z != 0;
+          const int act = p.act;
+          auto stage = [&](const uint32_t (&v)[32], int h, uint8_t* dst) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              uint4 o;
+              o.x = pack2(__uint_as_float(v[q * 8 + 0]), __uint_as_float(v[q * 8 + 1]), dtype);
+              o.y = pack2(__uint_as_float(v[q * 8 + 2]), __uint_as_float(v[q * 8 + 3]), dtype);
+              o.z = pack2(__uint_as_float(v[q * 8 + 4]), __uint_as_float(v[q * 8 + 5]), dtype);
+              o.w = pack2(__uint_as_float(v[q * 8 + 6]), __uint_as_float(v[q * 8 + 7]), dtype);
+              *reinterpret_cast<uint4*>(dst + (((h * 4 + q) ^ (lane & 7)) << 4)) = o;
+            }
+          };
+          auto emit = [&](uint32_t (&v)[32], int chunk, int h, uint8_t* zdst, uint8_t* ydst) {
+            if (p.bias != nullptr) {
+              const float4* bs = reinterpret_cast<const float4*>(bias_s + chunk * 32);
+#pragma unroll
+              for (int q = 0; q < 8; ++q) {
+                const float4 b4 = bs[q];  // warp-uniform address: a broadcast read
+                v[q * 4 + 0] = __float_as_uint(__uint_as_float(v[q * 4 + 0]) + b4.x);
+                v[q * 4 + 1] = __float_as_uint(__uint_as_float(v[q * 4 + 1]) + b4.y);
+                v[q * 4 + 2] = __float_as_uint(__uint_as_float(v[q * 4 + 2]) + b4.z);
+                v[q * 4 + 3] = __float_as_uint(__uint_as_float(v[q * 4 + 3]) + b4.w);
+              }
+            }
+            if (store_z) stage(v, h, zdst);
+            if (act == kActGeluNew) {
+#pragma unroll
+              for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(gelu_new(__uint_as_float(v[e])));
+            } else {
+#pragma unroll
+              for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(fmaxf(__uint_as_float(v[e]), 0.f));
+            }
+            stage(v, h, ydst);
+          };
+          uint32_t va[32], vb[32];
+          tmem_ld_32x32b_x32(tbase, va);
           for (int ci = 0; ci < nchunks; ci += 2) {
             const int col0 = n_blk * BN + ci * 32;
-            if (lane == 0) bulk_wait_group_read<0>();  // both staging buffers are rewritten below
+            const bool has_b = ci + 1 < nchunks;
+            // the staging buffer(s) about to be overwritten must have been read by their TMA stores
+            if (lane == 0) {
+              if (store_z) bulk_wait_group_read<0>(); else bulk_wait_group_read<1>();
+            }
             __syncwarp();
-            uint8_t* zdst = my_stage + lane * 128;
-            uint8_t* ydst = my_stage + EPI_BUF_BYTES + lane * 128;
-            for (int h = 0; h < 2 && ci + h < nchunks; ++h) {
-              tmem_ld_32x32b_x32(tbase + (ci + h) * 32, v);
+            uint8_t* zbuf = my_stage;
+            uint8_t* ybuf = my_stage + (store_z ? 1u : sbuf) * EPI_BUF_BYTES;
+            tmem_ld_wait();
+            if (has_b) tmem_ld_32x32b_x32(tbase + (ci + 1) * 32, vb);
+            emit(va, ci, 0, zbuf + lane * 128, ybuf + lane * 128);
+            if (has_b) {
               tmem_ld_wait();
-              const int c = col0 + h * 32;
-              if (p.bias != nullptr) {
-                const uint4* bp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.bias) + c);
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  if (c + q * 8 < p.N) {
-                    const uint4 bw = load_bias8(bp + q, p.N - (c + q * 8));
-                    const uint32_t w4[4] = {bw.x, bw.y, bw.z, bw.w};
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                      const float2 f = unpack2(w4[e], dtype);
-                      v[q * 8 + e * 2] = __float_as_uint(__uint_as_float(v[q * 8 + e * 2]) + f.x);
-                      v[q * 8 + e * 2 + 1] = __float_as_uint(__uint_as_float(v[q * 8 + e * 2 + 1]) + f.y);
-                    }
-                  }
-                }
-              }
-              if (p.store_z) {
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  uint4 o;
-                  o.x = pack2(__uint_as_float(v[q * 8 + 0]), __uint_as_float(v[q * 8 + 1]), dtype);
-                  o.y = pack2(__uint_as_float(v[q * 8 + 2]), __uint_as_float(v[q * 8 + 3]), dtype);
-                  o.z = pack2(__uint_as_float(v[q * 8 + 4]), __uint_as_float(v[q * 8 + 5]), dtype);
-                  o.w = pack2(__uint_as_float(v[q * 8 + 6]), __uint_as_float(v[q * 8 + 7]), dtype);
-                  *reinterpret_cast<uint4*>(zdst + (((h * 4 + q) ^ (lane & 7)) << 4)) = o;
-                }
-              }
-              if (p.act == kActGeluNew) {
-#pragma unroll
-                for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(gelu_new(__uint_as_float(v[e])));
-              } else if (p.act == kActRelu) {
-#pragma unroll
-                for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(fmaxf(__uint_as_float(v[e]), 0.f));
-              }
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                uint4 o;
-                o.x = pack2(__uint_as_float(v[q * 8 + 0]), __uint_as_float(v[q * 8 + 1]), dtype);
-                o.y = pack2(__uint_as_float(v[q * 8 + 2]), __uint_as_float(v[q * 8 + 3]), dtype);
-                o.z = pack2(__uint_as_float(v[q * 8 + 4]), __uint_as_float(v[q * 8 + 5]), dtype);
-                o.w = pack2(__uint_as_float(v[q * 8 + 6]), __uint_as_float(v[q * 8 + 7]), dtype);
-                *reinterpret_cast<uint4*>(ydst + (((h * 4 + q) ^ (lane & 7)) << 4)) = o;
-              }
+              if (ci + 2 < nchunks) tmem_ld_32x32b_x32(tbase + (ci + 2) * 32, va);
+              emit(vb, ci + 1, 1, zbuf + lane * 128, ybuf + lane * 128);
             }
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) {
-              if (p.store_z) tma_store_2d(&tmZ, my_stage, col0, rbase);
-              tma_store_2d(&tmD, my_stage + EPI_BUF_BYTES, col0, rbase);
+              if (store_z) tma_store_2d(&tmZ, zbuf, col0, rbase);
+              tma_store_2d(&tmD, ybuf, col0, rbase);
               bulk_commit_group();
             }
+            sbuf ^= 1u;
           }
         }
       } else if constexpr (!kMasked) {
@@ -496,19 +518,14 @@ __global__ void __launch_bounds__(THREADS, 1)
           const uint32_t tbase = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + buf * BN;
           auto emit = [&](uint32_t (&v)[32], int c, int h, uint8_t* sdst) {
             if (p.bias != nullptr) {
-              const uint4* bp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.bias) + c);
+              const float4* bs = reinterpret_cast<const float4*>(bias_s + (c - n_blk * BN));
 #pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                if (c + q * 8 < p.N) {
-                  const uint4 bw = load_bias8(bp + q, p.N - (c + q * 8));
-                  const uint32_t w4[4] = {bw.x, bw.y, bw.z, bw.w};
-#pragma unroll
-                  for (int e = 0; e < 4; ++e) {
-                    const float2 f = unpack2(w4[e], dtype);
-                    v[q * 8 + e * 2] = __float_as_uint(__uint_as_float(v[q * 8 + e * 2]) + f.x);
-                    v[q * 8 + e * 2 + 1] = __float_as_uint(__uint_as_float(v[q * 8 + e * 2 + 1]) + f.y);
-                  }
-                }
+              for (int q = 0; q < 8; ++q) {
+                const float4 b4 = bs[q];  // warp-uniform address: a broadcast read
+                v[q * 4 + 0] = __float_as_uint(__uint_as_float(v[q * 4 + 0]) + b4.x);
+                v[q * 4 + 1] = __float_as_uint(__uint_as_float(v[q * 4 + 1]) + b4.y);
+                v[q * 4 + 2] = __float_as_uint(__uint_as_float(v[q * 4 + 2]) + b4.z);
+                v[q * 4 + 3] = __float_as_uint(__uint_as_float(v[q * 4 + 3]) + b4.w);
               }
             }
 #pragma unroll
