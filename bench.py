@@ -52,6 +52,9 @@ def parse():
     ap.add_argument("--seq", type=int, default=0, help="model workloads: sequence length")
     ap.add_argument("--layers", type=int, default=0, help="model workloads: override the number of layers (debug)")
     ap.add_argument("--no-ckpt", action="store_true", help="model workloads: gradient checkpointing off")
+    ap.add_argument("--exchange", choices=["p2p", "nccl"], default="p2p",
+                    help="N > 1: adapter-gradient bucket averaged by the in-stream peer-memory kernel (default) or by "
+                         "NCCL all-reduce (layer workload: on a side stream overlapped with the next step; models: torch DDP)")
     ap.add_argument("--stock-head", action="store_true",
                     help="model workloads: keep torch's lm_head matmul and fp32 cross-entropy (default: lm_head through "
                          "the tcgen05 GEMM + fused cross-entropy, SURVEY 8f rows N2/N3)")
@@ -195,8 +198,11 @@ def run_point(a, pkg, rank, world, device, with_e2e=True):
     buckets = [torch.empty(r * K + N * r, device=device) for _ in range(2)]
     pending = [None, None]
     dist_on = world > 1
+    exch = None
     if dist_on:
         import torch.distributed as dist
+        if a.exchange == "p2p":
+            exch = pkg.comm.PeerBucketExchange(r * K + N * r)
 
     def step(i):
         bkt = buckets[i & 1]
@@ -207,7 +213,9 @@ def run_point(a, pkg, rank, world, device, with_e2e=True):
         Y, H, keep, xd = bind.linear_fwd(x, W, b, A, B, s, p, 1, 4 * i, a.conv1d, ws, save_xd=True)
         bind.linear_bwd(dy, xd if xd is not None else x, W, A, B, H, keep, s, p, a.conv1d, ws, need_dx=True, dA=dA,
                         dB=dB, x_is_dropped=xd is not None)
-        if dist_on:  # the path's one exchange step under DDP: average the adapter gradients
+        if exch is not None:  # the path's one exchange step under DDP: average the adapter gradients, in stream
+            exch.allreduce_avg_(bkt)
+        elif dist_on:
             pending[i & 1] = dist.all_reduce(bkt, op=dist.ReduceOp.AVG, async_op=True)
         return Y
 
@@ -332,8 +340,11 @@ def run_point(a, pkg, rank, world, device, with_e2e=True):
                    "l2_policy": "inputs larger than L2 (X, dY, Y, dX, W = %.0f MB per step vs 126 MB L2)" %
                                 ((3 * M * K + 2 * M * N + K * N) * 2 / 1e6 if K == N else
                                  (2 * M * K + 2 * M * N + K * N) * 2 / 1e6),
-                   "exchange": "NCCL all-reduce(avg) of the flat adapter-grad bucket every step, overlapped with the next step's compute (two buckets)" if dist_on else "none"},
-        "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 7 * a.steps, "roofline": roofline,
+                   "exchange": ("none" if not dist_on else
+                                "in-stream peer-memory all-reduce(avg) of the flat adapter-grad bucket every step (csrc/p2p.cuh)"
+                                if exch is not None else
+                                "NCCL all-reduce(avg) of the flat adapter-grad bucket every step, overlapped with the next step's compute (two buckets)")},
+        "clocks": clk.summary(), "e2e": e2e, "gpu_launches": (7 + (1 if exch is not None else 0)) * a.steps, "roofline": roofline,
     }
     return line
 
@@ -361,7 +372,7 @@ def model_spec(a):
 def model_workload_name(a, B, S, world):
     return (f"{a.workload} architecture (random init) LoRA r=8 alpha=16 dropout=0.05 fine-tune step, "
             f"gradient checkpointing {'off' if a.no_ckpt else 'on'}, batch {B} x seq {S} per GPU, "
-            f"{'DDP over NCCL, ' if world > 1 else ''}AdamW lr 5e-5 + clip 1.0, "
+            f"{('DDP, adapter bucket averaged by ' + ('the in-stream peer-memory kernel, ' if a.exchange == 'p2p' else 'NCCL all-reduce, ')) if world > 1 else ''}AdamW lr 5e-5 + clip 1.0, "
             f"{'stock torch lm_head + fp32 CE' if a.stock_head else 'lm_head on the tcgen05 GEMM + fused CE'}")
 
 
@@ -384,7 +395,7 @@ def run_model(a, pkg, rank, world, device):
         pkg.frozen.accelerate_lm_head(pm)
         pkg.frozen.accelerate_frozen_neighbours(pm)
         loss_fn = pkg.frozen.fused_causal_lm_loss
-    net = pkg.train.wrap_ddp(pm, device) if world > 1 else pm
+    net = pkg.train.wrap_ddp(pm, device, exchange=a.exchange) if world > 1 else pm
     tr = pkg.train.Trainer(net, pkg.train.TrainConfig(lr=5e-5, accum=1, total_steps=10 ** 6), loss_fn=loss_fn)
     tr._ensure_sched(10 ** 6)
     net.train()

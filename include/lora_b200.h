@@ -167,6 +167,32 @@ int lora_act_bwd(const void* dY, const void* ZorY, void* dZ, int64_t n_elems, in
                  cudaStream_t stream);
 
 /*
+ * The path's one exchange step under DDP: average the flat fp32 adapter-gradient bucket (dA|dB of every
+ * adapted layer) over the GPUs of one NVLink/NVSwitch box, in the caller's stream, through peer memory.
+ * Replaces the gloo/NCCL all-reduce torch DDP issues for the reference
+ * (finetune_lora_distilgpt2.py:142, ddp_find_unused_parameters=False).  One process per GPU.
+ *   lora_p2p_alloc   allocates this rank's exchange buffer (lora_p2p_buffer_bytes(capacity)), zeroes it and
+ *                    returns its 64-byte CUDA IPC handle; the host exchanges the handles (any side channel)
+ *   lora_p2p_open    maps a peer's buffer;  lora_p2p_close / lora_p2p_free undo the two
+ *   lora_bucket_allreduce_avg  bucket[i] <- mean over ranks, in place.  syms[q] (host array, q < world) is
+ *                    rank q's buffer as mapped in THIS process (syms[rank] = own).  seq = 1, 2, 3, ... must
+ *                    advance by one per call, identically on every rank; calls are collective and
+ *                    stream-ordered, no host synchronisation.  Every rank sums in rank order, so all ranks
+ *                    get the bit-identical result.  mode 0 picks one-shot (small buckets) or two-shot
+ *                    (reduce my slice, push it to every peer) by size.
+ * A rank that never calls trips the device watchdog (trap after 2^33 cycles) on its peers.
+ */
+#define LORA_P2P_HANDLE_BYTES 64
+#define LORA_P2P_MAX_WORLD 8
+size_t lora_p2p_buffer_bytes(int64_t capacity_floats);
+int lora_p2p_alloc(int64_t capacity_floats, void** sym, void* ipc_handle_out);
+int lora_p2p_open(const void* ipc_handle, void** peer_sym);
+int lora_p2p_close(void* peer_sym);
+int lora_p2p_free(void* sym);
+int lora_bucket_allreduce_avg(float* bucket, int64_t n, void* const* syms, int32_t rank, int32_t world,
+                              int64_t capacity_floats, uint32_t seq, int32_t mode, cudaStream_t stream);
+
+/*
  * Token cross-entropy from 16-bit logits; replaces the fp32 logits copy +
  * log_softmax + nll_loss that the HF causal-LM loss runs on DataCollatorForLanguageModeling labels
  * (finetune_lora_distilgpt2.py:114) and nn.CrossEntropyLoss in finetune_lora_opt_pp.py:143-153.

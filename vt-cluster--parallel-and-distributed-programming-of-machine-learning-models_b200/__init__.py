@@ -9,6 +9,7 @@ from . import lora  # noqa: F401
 from . import train  # noqa: F401
 from . import pipeline  # noqa: F401
 from . import frozen  # noqa: F401
+from . import comm  # noqa: F401
 from .api import (  # noqa: F401
     LoraConfig,
     LoraModel,
@@ -23,5 +24,5 @@ from ._build import build  # noqa: F401
 
 __all__ = [
     "LoraConfig", "LoraModel", "PeftModel", "PeftModelForCausalLM", "PeftType", "TaskType", "get_peft_model",
-    "fused_lora_linear", "binding", "lora", "train", "pipeline", "frozen", "build",
+    "fused_lora_linear", "binding", "lora", "train", "pipeline", "frozen", "comm", "build",
 ]

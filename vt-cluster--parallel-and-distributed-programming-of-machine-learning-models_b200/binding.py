@@ -8,7 +8,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_uint64, c_void_p
+from ctypes import c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_uint32, c_uint64, c_void_p
 
 import torch
 
@@ -43,6 +43,13 @@ _SIGNATURES = {
     "lora_frozen_linear_act_fwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int64,
                                            c_int64, c_int64, c_int32, c_int32, c_int32, c_void_p]),
     "lora_act_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p]),
+    "lora_p2p_buffer_bytes": (c_size_t, [c_int64]),
+    "lora_p2p_alloc": (c_int, [c_int64, ctypes.POINTER(c_void_p), c_void_p]),
+    "lora_p2p_open": (c_int, [c_void_p, ctypes.POINTER(c_void_p)]),
+    "lora_p2p_close": (c_int, [c_void_p]),
+    "lora_p2p_free": (c_int, [c_void_p]),
+    "lora_bucket_allreduce_avg": (c_int, [c_void_p, c_int64, ctypes.POINTER(c_void_p), c_int32, c_int32, c_int64, c_uint32,
+                                          c_int32, c_void_p]),
     "lora_ce_fwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int32, c_void_p]),
     "lora_ce_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64,
                             c_int32, c_void_p]),

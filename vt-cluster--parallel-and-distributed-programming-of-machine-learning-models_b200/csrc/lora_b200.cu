@@ -14,6 +14,7 @@
 
 #include "act.cuh"
 #include "ce.cuh"
+#include "p2p.cuh"
 #include "gemm_sm100.cuh"
 #include "lora_b200.h"
 #include "skinny.cuh"
@@ -727,6 +728,84 @@ int lora_ce_bwd(const void* logits, int64_t ld, const int64_t* labels, const flo
   CUDA_TRY(launch_pdl(ce::ce_bwd_kernel, dim3((unsigned)M), dim3(ce::THREADS), 0, stream, 1,
                       static_cast<const uint16_t*>(logits), (long long)ld, reinterpret_cast<const long long*>(labels), lse,
                       grad_scale, static_cast<uint16_t*>(dlogits), (long long)ldd, (int)V, (long long)ignore_index, (int)dtype));
+  return 0;
+}
+
+// ---- peer-memory exchange of the adapter-gradient bucket (p2p.cuh) ----
+size_t lora_p2p_buffer_bytes(int64_t capacity_floats) {
+  if (capacity_floats <= 0) return 0;
+  const size_t cap = (static_cast<size_t>(capacity_floats) + 63) & ~size_t(63);
+  return p2p::CTRL_BYTES + 4 * cap * sizeof(float);
+}
+
+int lora_p2p_alloc(int64_t capacity_floats, void** sym, void* ipc_handle_out) {
+  g_err.clear();
+  if (!sym || !ipc_handle_out || capacity_floats <= 0) return fail("lora_p2p_alloc: bad argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == LORA_P2P_HANDLE_BYTES, "handle size");
+  void* p = nullptr;
+  const size_t bytes = lora_p2p_buffer_bytes(capacity_floats);
+  CUDA_TRY(cudaMalloc(&p, bytes));
+  cudaError_t e = cudaMemset(p, 0, bytes);  // flags and arrival counters start at zero; sequence numbers start at 1
+  cudaIpcMemHandle_t h;
+  if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    return fail("lora_p2p_alloc: %s", cudaGetErrorString(e));
+  }
+  std::memcpy(ipc_handle_out, &h, sizeof(h));
+  *sym = p;
+  return 0;
+}
+
+int lora_p2p_open(const void* ipc_handle, void** peer_sym) {
+  g_err.clear();
+  if (!ipc_handle || !peer_sym) return fail("lora_p2p_open: null argument");
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, ipc_handle, sizeof(h));
+  void* p = nullptr;
+  cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) return fail("lora_p2p_open: cudaIpcOpenMemHandle: %s (peer GPUs must be P2P-capable, one process per GPU)", cudaGetErrorString(e));
+  *peer_sym = p;
+  return 0;
+}
+
+int lora_p2p_close(void* peer_sym) {
+  g_err.clear();
+  if (peer_sym) CUDA_TRY(cudaIpcCloseMemHandle(peer_sym));
+  return 0;
+}
+
+int lora_p2p_free(void* sym) {
+  g_err.clear();
+  if (sym) CUDA_TRY(cudaFree(sym));
+  return 0;
+}
+
+int lora_bucket_allreduce_avg(float* bucket, int64_t n, void* const* syms, int32_t rank, int32_t world,
+                              int64_t capacity_floats, uint32_t seq, int32_t mode, cudaStream_t stream) {
+  g_err.clear();
+  if (!bucket || !syms) return fail("lora_bucket_allreduce_avg: null argument");
+  if (world < 1 || world > p2p::MAX_WORLD || rank < 0 || rank >= world) return fail("lora_bucket_allreduce_avg: world must be 1..%d and 0 <= rank < world", p2p::MAX_WORLD);
+  if (n <= 0 || n > capacity_floats) return fail("lora_bucket_allreduce_avg: %lld values do not fit the exchange buffers (%lld)", (long long)n, (long long)capacity_floats);
+  if (seq == 0) return fail("lora_bucket_allreduce_avg: sequence numbers start at 1 (0 is the buffers' initial state)");
+  if (reinterpret_cast<uintptr_t>(bucket) & 15) return fail("lora_bucket_allreduce_avg: bucket must be 16-byte aligned");
+  if (mode < 0 || mode > 2) return fail("lora_bucket_allreduce_avg: mode is 0 (auto), 1 (one-shot) or 2 (two-shot)");
+  if (world == 1) return 0;
+  int sms = 0;
+  if (device_setup(&sms)) return 1;
+  p2p::Peers peers{};
+  for (int q = 0; q < world; ++q) {
+    if (!syms[q]) return fail("lora_bucket_allreduce_avg: syms[%d] is null", q);
+    peers.sym[q] = syms[q];
+  }
+  const long long cap = (static_cast<long long>(capacity_floats) + 63) & ~63LL;
+  int two_shot = mode == 2 || (mode == 0 && world > 2 && n * 4 > (1 << 20));
+  if (n % 4) two_shot = 0;
+  const long long work4 = two_shot ? (n / 4 + world - 1) / world : (n + 3) / 4;
+  const int grid = static_cast<int>(std::max<long long>(1, std::min<long long>((work4 + p2p::THREADS - 1) / p2p::THREADS, p2p::MAX_CTAS)));
+  CUDA_TRY(launch_pdl(p2p::bucket_allreduce_kernel, dim3(grid), dim3(p2p::THREADS), 0, stream, 1, bucket, (long long)n, peers,
+                      (int)rank, (int)world, seq, cap, two_shot));
   return 0;
 }
 

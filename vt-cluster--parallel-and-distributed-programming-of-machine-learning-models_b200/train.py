@@ -62,17 +62,29 @@ def trainable_parameters(model: nn.Module):
 
 
 def wrap_ddp(model: nn.Module, device: Optional[torch.device] = None, bucket_cap_mb: int = 25,
-             static_graph: bool = False) -> nn.Module:
+             static_graph: bool = False, exchange: str = "nccl") -> nn.Module:
     """torch DDP the way HF Trainer configures it for the reference
     (ddp_find_unused_parameters=False, finetune_lora_distilgpt2.py:142): frozen base weights
     never enter the reducer, so the only traffic is the adapter-gradient bucket
-    (1.6 MB for distilgpt2 r=8)."""
+    (1.6 MB for distilgpt2 r=8).  exchange="p2p" (CUDA only) replaces the NCCL all-reduce of each
+    bucket by the in-stream peer-memory kernel of comm.PeerBucketExchange."""
     from torch.nn.parallel import DistributedDataParallel as DDP
 
     kw = dict(find_unused_parameters=False, bucket_cap_mb=bucket_cap_mb, gradient_as_bucket_view=True,
               static_graph=static_graph)
+    if exchange not in ("nccl", "p2p"):
+        raise ValueError("exchange must be 'nccl' or 'p2p'")
     if device is not None and device.type == "cuda":
-        return DDP(model, device_ids=[device.index], output_device=device.index, **kw)
+        ddp = DDP(model, device_ids=[device.index], output_device=device.index, **kw)
+        if exchange == "p2p":
+            from .comm import PeerBucketExchange
+
+            n = sum(p.numel() for p in model.parameters() if p.requires_grad)
+            ddp._lora_exchange = PeerBucketExchange(n)  # kept alive with the wrapper
+            ddp.register_comm_hook(None, ddp._lora_exchange.ddp_hook)
+        return ddp
+    if exchange == "p2p":
+        raise RuntimeError("exchange='p2p' needs CUDA devices (no CPU fallback)")
     return DDP(model, **kw)
 
 
