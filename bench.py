@@ -55,6 +55,8 @@ def parse():
     ap.add_argument("--exchange", choices=["p2p", "nccl"], default="p2p",
                     help="N > 1: adapter-gradient bucket averaged by the in-stream peer-memory kernel (default) or by "
                          "NCCL all-reduce (layer workload: on a side stream overlapped with the next step; models: torch DDP)")
+    ap.add_argument("--no-graph", action="store_true",
+                    help="layer workload: launch every step eagerly instead of replaying one captured CUDA graph per step")
     ap.add_argument("--stock-head", action="store_true",
                     help="model workloads: keep torch's lm_head matmul and fp32 cross-entropy (default: lm_head through "
                          "the tcgen05 GEMM + fused cross-entropy, SURVEY 8f rows N2/N3)")
@@ -230,15 +232,51 @@ def run_point(a, pkg, rank, world, device, with_e2e=True):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # One step = one CUDA-graph replay (launch-bound inner loop captured once; 8 processes launching 8 kernels
+    # every 0.4 ms from Python otherwise sit on the critical path).  The dropout offset advances on the device
+    # inside the graph (lora_linear_fwd_devrng), the exchange kernel keeps its call counter on the device, so
+    # every replay draws a fresh mask and is a complete step.  NCCL mode stays eager (side-stream overlap).
+    graph = None
+    rng_dev = torch.zeros(1, dtype=torch.int64, device=device)
+    bkt0 = buckets[0]
+    dA0, dB0 = bkt0[: r * K].view(r, K), bkt0[r * K:].view(N, r)
+
+    def graph_step():
+        Y, H, keep, xd = bind.linear_fwd(x, W, b, A, B, s, p, 1, 0, a.conv1d, ws, save_xd=True, offset_dev=rng_dev)
+        bind.linear_bwd(dy, xd if xd is not None else x, W, A, B, H, keep, s, p, a.conv1d, ws, need_dx=True, dA=dA0,
+                        dB=dB0, x_is_dropped=xd is not None)
+        if exch is not None:
+            exch.allreduce_avg_(bkt0)
+        rng_dev.add_(4)
+
+    if not a.no_graph and (exch is not None or not dist_on):
+        try:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(3):
+                    graph_step()
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                graph_step()
+        except Exception as e:  # noqa: BLE001
+            print(f"[bench] CUDA-graph capture failed ({e!r}); running eagerly", file=sys.stderr)
+            graph = None
+            if dist_on:
+                raise  # ranks must not diverge between graph and eager paths
+
+    run_step = (lambda i: graph.replay()) if graph is not None else step
     for i in range(a.warmup):
-        step(i)
+        run_step(i)
     drain()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(torch.cuda.current_device()) as clk:
         e0.record()
         for i in range(a.steps):
-            step(i)
+            run_step(i)
         drain()  # every all-reduce is inside the timed region
         e1.record()
         barrier()
@@ -340,6 +378,7 @@ def run_point(a, pkg, rank, world, device, with_e2e=True):
                    "l2_policy": "inputs larger than L2 (X, dY, Y, dX, W = %.0f MB per step vs 126 MB L2)" %
                                 ((3 * M * K + 2 * M * N + K * N) * 2 / 1e6 if K == N else
                                  (2 * M * K + 2 * M * N + K * N) * 2 / 1e6),
+                   "launch": "one CUDA-graph replay per step" if graph is not None else "eager",
                    "exchange": ("none" if not dist_on else
                                 "in-stream peer-memory all-reduce(avg) of the flat adapter-grad bucket every step (csrc/p2p.cuh)"
                                 if exch is not None else

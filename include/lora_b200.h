@@ -68,6 +68,18 @@ int lora_linear_fwd(const void* X, const void* W, const void* bias, const float*
                     size_t workspace_bytes, cudaStream_t stream);
 
 /*
+ * lora_linear_fwd whose dropout offset also has a device-side part: the Philox offset used is
+ * offset + *offset_dev (offset_dev: device pointer to one uint64, NULL = 0), read when the kernel runs.
+ * A training step captured in a CUDA graph advances *offset_dev inside the graph and so draws a fresh
+ * mask on every replay -- the role of torch's graph-safe generator state for torch's own dropout
+ * (the reference's lora_dropout is torch.nn.Dropout inside peft's lora.Linear).  No other difference.
+ */
+int lora_linear_fwd_devrng(const void* X, const void* W, const void* bias, const float* A, const float* B, void* Y, void* H,
+                           uint8_t* keep_mask, void* Xd, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p,
+                           uint64_t seed, uint64_t offset, const uint64_t* offset_dev, int32_t dtype, int32_t w_is_KN,
+                           void* workspace, size_t workspace_bytes, cudaStream_t stream);
+
+/*
  * Backward of the same projection; replaces what torch autograd derives from
  * peft's forward (no custom backward exists in the reference):
  *     dH = scaling * dY B                 dX = dY W + keep/(1-p) .* (dH A)
@@ -175,9 +187,9 @@ int lora_act_bwd(const void* dY, const void* ZorY, void* dZ, int64_t n_elems, in
  *                    returns its 64-byte CUDA IPC handle; the host exchanges the handles (any side channel)
  *   lora_p2p_open    maps a peer's buffer;  lora_p2p_close / lora_p2p_free undo the two
  *   lora_bucket_allreduce_avg  bucket[i] <- mean over ranks, in place.  syms[q] (host array, q < world) is
- *                    rank q's buffer as mapped in THIS process (syms[rank] = own).  seq = 1, 2, 3, ... must
- *                    advance by one per call, identically on every rank; calls are collective and
- *                    stream-ordered, no host synchronisation.  Every rank sums in rank order, so all ranks
+ *                    rank q's buffer as mapped in THIS process (syms[rank] = own).  Calls are collective (every
+ *                    rank makes the same sequence of calls; the call counter lives in the buffers, on the
+ *                    device) and stream-ordered, no host synchronisation.  Every rank sums in rank order, so all ranks
  *                    get the bit-identical result.  mode 0 picks one-shot (small buckets) or two-shot
  *                    (reduce my slice, push it to every peer) by size.
  * A rank that never calls trips the device watchdog (trap after 2^33 cycles) on its peers.
@@ -190,7 +202,7 @@ int lora_p2p_open(const void* ipc_handle, void** peer_sym);
 int lora_p2p_close(void* peer_sym);
 int lora_p2p_free(void* sym);
 int lora_bucket_allreduce_avg(float* bucket, int64_t n, void* const* syms, int32_t rank, int32_t world,
-                              int64_t capacity_floats, uint32_t seq, int32_t mode, cudaStream_t stream);
+                              int64_t capacity_floats, int32_t mode, cudaStream_t stream);
 
 /*
  * Token cross-entropy from 16-bit logits; replaces the fp32 logits copy +

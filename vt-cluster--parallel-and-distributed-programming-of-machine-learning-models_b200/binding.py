@@ -28,6 +28,11 @@ _SIGNATURES = {
         [c_void_p] * 9 + [c_int64, c_int64, c_int64, c_int32, c_float, c_float, c_uint64, c_uint64, c_int32, c_int32,
                           c_void_p, c_size_t, c_void_p],
     ),
+    "lora_linear_fwd_devrng": (
+        c_int,
+        [c_void_p] * 9 + [c_int64, c_int64, c_int64, c_int32, c_float, c_float, c_uint64, c_uint64, c_void_p, c_int32, c_int32,
+                          c_void_p, c_size_t, c_void_p],
+    ),
     "lora_linear_bwd": (
         c_int,
         [c_void_p] * 10 + [c_int64, c_int64, c_int64, c_int32, c_float, c_float, c_int32, c_int32, c_int32, c_int32,
@@ -48,8 +53,8 @@ _SIGNATURES = {
     "lora_p2p_open": (c_int, [c_void_p, ctypes.POINTER(c_void_p)]),
     "lora_p2p_close": (c_int, [c_void_p]),
     "lora_p2p_free": (c_int, [c_void_p]),
-    "lora_bucket_allreduce_avg": (c_int, [c_void_p, c_int64, ctypes.POINTER(c_void_p), c_int32, c_int32, c_int64, c_uint32,
-                                          c_int32, c_void_p]),
+    "lora_bucket_allreduce_avg": (c_int, [c_void_p, c_int64, ctypes.POINTER(c_void_p), c_int32, c_int32, c_int64, c_int32,
+                                          c_void_p]),
     "lora_ce_fwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int32, c_void_p]),
     "lora_ce_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64,
                             c_int32, c_void_p]),
@@ -115,9 +120,11 @@ def workspace_bytes(M: int, K: int, N: int, r: int) -> int:
     return int(lib().lora_linear_workspace_bytes(M, K, N, r))
 
 
-def linear_fwd(x2d, W, bias, A, B, scaling, p, seed, offset, w_is_KN, workspace, out=None, save_xd=False):
+def linear_fwd(x2d, W, bias, A, B, scaling, p, seed, offset, w_is_KN, workspace, out=None, save_xd=False,
+               offset_dev=None):
     """Y, H, keep[, Xd] = fused forward.  x2d [M,K] 16-bit, A [r,K] / B [N,r] fp32.
-    save_xd: also return keep .* X (None when p == 0) for linear_bwd(..., x_is_dropped=True)."""
+    save_xd: also return keep .* X (None when p == 0) for linear_bwd(..., x_is_dropped=True).
+    offset_dev: optional int64/uint64 CUDA scalar added to `offset` on the device (CUDA-graph replay)."""
     _need_cuda(x2d, W, bias, A, B, workspace)
     M, K = x2d.shape
     N = W.shape[1] if w_is_KN else W.shape[0]
@@ -126,10 +133,12 @@ def linear_fwd(x2d, W, bias, A, B, scaling, p, seed, offset, w_is_KN, workspace,
     H = torch.empty((M, rpad(r)), dtype=x2d.dtype, device=x2d.device)
     keep = torch.empty((M, K // 8), dtype=torch.uint8, device=x2d.device) if p > 0 else None
     xd = torch.empty_like(x2d) if (save_xd and p > 0) else None
-    rc = lib().lora_linear_fwd(
+    if offset_dev is not None and (not offset_dev.is_cuda or offset_dev.element_size() != 8):
+        raise RuntimeError("offset_dev must be a 64-bit integer CUDA tensor")
+    rc = lib().lora_linear_fwd_devrng(
         _ptr(x2d), _ptr(W), _ptr(bias), _ptr(A), _ptr(B), _ptr(Y), _ptr(H), _ptr(keep), _ptr(xd), M, K, N, r,
         float(scaling),
-        float(p), int(seed), int(offset), dtype_code(x2d.dtype), int(bool(w_is_KN)), _ptr(workspace),
+        float(p), int(seed), int(offset), _ptr(offset_dev), dtype_code(x2d.dtype), int(bool(w_is_KN)), _ptr(workspace),
         workspace.numel() * workspace.element_size(), _stream(),
     )
     _check(rc, "lora_linear_fwd")

@@ -34,7 +34,6 @@ class PeerBucketExchange:
         if self.world > MAX_WORLD:
             raise RuntimeError(f"PeerBucketExchange spans one box: at most {MAX_WORLD} ranks, got {self.world}")
         self.capacity = int(capacity_floats)
-        self.seq = 0
         self._lib = binding.lib()
         self._own = ctypes.c_void_p()
         handle = ctypes.create_string_buffer(64)
@@ -57,9 +56,8 @@ class PeerBucketExchange:
         """t <- mean over ranks, in place, enqueued on the current stream (fp32, contiguous, CUDA)."""
         if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
             raise RuntimeError("allreduce_avg_ needs a contiguous fp32 CUDA tensor")
-        self.seq += 1
         rc = self._lib.lora_bucket_allreduce_avg(ctypes.c_void_p(t.data_ptr()), t.numel(), self._syms, self.rank, self.world,
-                                                 self.capacity, self.seq, mode,
+                                                 self.capacity, mode,
                                                  ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
         binding._check(rc, "lora_bucket_allreduce_avg")
         return t

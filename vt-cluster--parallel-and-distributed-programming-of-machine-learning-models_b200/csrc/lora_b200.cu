@@ -237,7 +237,8 @@ int launch_rowproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmP, const CUt
 
 // out[M, rp] = out_scale * (keep .* act)[M, C] * P[rp, C]^T
 int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out, void* xd_out, int64_t M, int64_t C,
-                   int rp, int dtype, float out_scale, float p, uint64_t seed, uint64_t offset, cudaStream_t stream) {
+                   int rp, int dtype, float out_scale, float p, uint64_t seed, uint64_t offset, cudaStream_t stream,
+                   const uint64_t* offset_dev = nullptr) {
   CUtensorMap tmAct, tmP, tmXd;
   if (make_tmap(&tmAct, act, dtype, C, M, C, skinny::RP_BK, skinny::rp_rows(rp), CU_TENSOR_MAP_SWIZZLE_128B, "rowproj act")) return 1;
   if (make_tmap(&tmP, P, dtype, C, rp, C, skinny::RP_BK, rp, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj P")) return 1;
@@ -256,6 +257,7 @@ int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out,
   rp_p.dropout = p > 0.f ? 1 : 0;
   rp_p.seed = seed;
   rp_p.offset = offset;
+  rp_p.offset_dev = reinterpret_cast<const unsigned long long*>(offset_dev);
   rp_p.thresh14 = static_cast<uint32_t>(p * 16384.0f + 0.5f);
   const bool bf = dtype == kDtypeBf16;
 #define RP_CASE(BF, RP) return launch_rowproj_t<BF, RP>(tmAct, tmP, tmXd, rp_p, stream);
@@ -487,6 +489,14 @@ int lora_linear_fwd(const void* X, const void* W, const void* bias, const float*
                     uint8_t* keep_mask, void* Xd, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p,
                     uint64_t seed, uint64_t offset, int32_t dtype, int32_t w_is_KN, void* workspace,
                     size_t workspace_bytes, cudaStream_t stream) {
+  return lora_linear_fwd_devrng(X, W, bias, A, B, Y, H, keep_mask, Xd, M, K, N, r, scaling, p, seed, offset, nullptr, dtype,
+                                w_is_KN, workspace, workspace_bytes, stream);
+}
+
+int lora_linear_fwd_devrng(const void* X, const void* W, const void* bias, const float* A, const float* B, void* Y, void* H,
+                           uint8_t* keep_mask, void* Xd, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p,
+                           uint64_t seed, uint64_t offset, const uint64_t* offset_dev, int32_t dtype, int32_t w_is_KN,
+                           void* workspace, size_t workspace_bytes, cudaStream_t stream) {
   g_err.clear();
   if (check_common(M, K, N, r, dtype)) return 1;
   if (!X || !W || !A || !B || !Y || !H || !workspace) return fail("lora_linear_fwd: null pointer argument");
@@ -502,7 +512,7 @@ int lora_linear_fwd(const void* X, const void* W, const void* bias, const float*
 
   if (phase_on(kPhasePack) && launch_pack(A, B, ws, w, K, N, r, scaling, dtype, stream)) return 1;
   if (phase_on(kPhaseRowProj) &&
-      launch_rowproj(X, ws + w.a16, H, keep_mask, Xd, M, K, rp, dtype, inv_keep, p, seed, offset, stream))
+      launch_rowproj(X, ws + w.a16, H, keep_mask, Xd, M, K, rp, dtype, inv_keep, p, seed, offset, stream, offset_dev))
     return 1;
   if (!phase_on(kPhaseGemm)) return 0;
   GemmArgs g{};
@@ -745,7 +755,7 @@ int lora_p2p_alloc(int64_t capacity_floats, void** sym, void* ipc_handle_out) {
   void* p = nullptr;
   const size_t bytes = lora_p2p_buffer_bytes(capacity_floats);
   CUDA_TRY(cudaMalloc(&p, bytes));
-  cudaError_t e = cudaMemset(p, 0, bytes);  // flags and arrival counters start at zero; sequence numbers start at 1
+  cudaError_t e = cudaMemset(p, 0, bytes);  // flags, arrival counters and the sequence counter start at zero
   cudaIpcMemHandle_t h;
   if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
@@ -783,12 +793,11 @@ int lora_p2p_free(void* sym) {
 }
 
 int lora_bucket_allreduce_avg(float* bucket, int64_t n, void* const* syms, int32_t rank, int32_t world,
-                              int64_t capacity_floats, uint32_t seq, int32_t mode, cudaStream_t stream) {
+                              int64_t capacity_floats, int32_t mode, cudaStream_t stream) {
   g_err.clear();
   if (!bucket || !syms) return fail("lora_bucket_allreduce_avg: null argument");
   if (world < 1 || world > p2p::MAX_WORLD || rank < 0 || rank >= world) return fail("lora_bucket_allreduce_avg: world must be 1..%d and 0 <= rank < world", p2p::MAX_WORLD);
   if (n <= 0 || n > capacity_floats) return fail("lora_bucket_allreduce_avg: %lld values do not fit the exchange buffers (%lld)", (long long)n, (long long)capacity_floats);
-  if (seq == 0) return fail("lora_bucket_allreduce_avg: sequence numbers start at 1 (0 is the buffers' initial state)");
   if (reinterpret_cast<uintptr_t>(bucket) & 15) return fail("lora_bucket_allreduce_avg: bucket must be 16-byte aligned");
   if (mode < 0 || mode > 2) return fail("lora_bucket_allreduce_avg: mode is 0 (auto), 1 (one-shot) or 2 (two-shot)");
   if (world == 1) return 0;
@@ -805,7 +814,7 @@ int lora_bucket_allreduce_avg(float* bucket, int64_t n, void* const* syms, int32
   const long long work4 = two_shot ? (n / 4 + world - 1) / world : (n + 3) / 4;
   const int grid = static_cast<int>(std::max<long long>(1, std::min<long long>((work4 + p2p::THREADS - 1) / p2p::THREADS, p2p::MAX_CTAS)));
   CUDA_TRY(launch_pdl(p2p::bucket_allreduce_kernel, dim3(grid), dim3(p2p::THREADS), 0, stream, 1, bucket, (long long)n, peers,
-                      (int)rank, (int)world, seq, cap, two_shot));
+                      (int)rank, (int)world, cap, two_shot));
   return 0;
 }
 

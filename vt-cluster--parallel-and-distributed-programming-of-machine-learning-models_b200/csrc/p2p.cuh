@@ -16,6 +16,9 @@
 //   local copy result[parity] -> bucket.  Per rank (world-1)/world * 2n values cross NVLink instead of
 //   (world-1) * n.
 //
+// The sequence number of a call lives in Ctrl (starts at 0, the published count): no host-side state,
+// so the launch can sit in a CUDA graph that is replayed.
+//
 // Why two parities are enough with one flag round per call: a rank overwrites data[parity] two calls
 // later, after it has passed the flag wait of the call in between -- which every peer enters only after
 // finishing its reads of this call (kernels of one stream run in order).  Flags compare with ==, and a
@@ -39,6 +42,8 @@ struct Ctrl {
   uint32_t flag_a[2][MAX_WORLD];  // [parity][source rank] = seq: source's data[parity] is complete
   uint32_t flag_b[2][MAX_WORLD];  // [parity][source rank] = seq: source's slice sits in my result[parity]
   uint32_t arrive[2][2];          // [parity][round]: CTAs of THIS rank that finished the round (self-resetting)
+  uint32_t seq;                   // number of exchanges this rank has published (advances on the device, so a
+                                  // captured CUDA graph can be replayed); identical on all ranks by construction
 };
 static_assert(sizeof(Ctrl) <= CTRL_BYTES, "control block");
 
@@ -75,6 +80,7 @@ __device__ __forceinline__ void publish_and_wait(const Peers& peers, int rank, i
     const uint32_t prev = atomicAdd(&mine->arrive[parity][round], 1u);
     if (prev == gridDim.x - 1) {
       mine->arrive[parity][round] = 0u;  // next use is two calls away
+      if (round == 0) mine->seq = seq;   // every CTA of this launch has read the old value by now
       __threadfence_system();
       for (int q = 0; q < world; ++q) {
         Ctrl* c = reinterpret_cast<Ctrl*>(peers.sym[q]);
@@ -97,9 +103,10 @@ __device__ __forceinline__ void publish_and_wait(const Peers& peers, int rank, i
 }
 
 __global__ void __launch_bounds__(THREADS)
-    bucket_allreduce_kernel(float* __restrict__ bucket, long long n, const Peers peers, int rank, int world, uint32_t seq,
+    bucket_allreduce_kernel(float* __restrict__ bucket, long long n, const Peers peers, int rank, int world,
                             long long cap, int two_shot) {
   pdl_wait();  // the bucket is written by the kernels before this one in the stream
+  const uint32_t seq = *reinterpret_cast<volatile const uint32_t*>(&reinterpret_cast<const Ctrl*>(peers.sym[rank])->seq) + 1u;
   const int parity = static_cast<int>(seq & 1u);
   const long long n4 = n >> 2;
   const long long tid = blockIdx.x * static_cast<long long>(THREADS) + threadIdx.x;

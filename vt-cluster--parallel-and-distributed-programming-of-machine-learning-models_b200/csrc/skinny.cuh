@@ -143,6 +143,7 @@ struct RowProjParams {
   int dropout;  // 0/1
   int store_xd;  // 1: TMA-store the masked tiles (keep .* Act, unscaled) through tmXd
   uint64_t seed, offset;
+  const unsigned long long* offset_dev;  // optional: *offset_dev is added to `offset` (graph-replayable RNG state)
   uint32_t thresh14;  // round(p * 16384)
 };
 
@@ -211,7 +212,8 @@ __global__ void __launch_bounds__(rp_threads(kRPad))
   uint64_t gbase[2] = {0, 0};
   bool row_ok[2] = {false, false};
   const uint32_t thresh2 = dropout_thresh_half2(p.thresh14);
-  const uint32_t off_lo = static_cast<uint32_t>(p.offset), off_hi = static_cast<uint32_t>(p.offset >> 32);
+  const uint64_t offset = p.offset + ((p.dropout && p.offset_dev != nullptr) ? *p.offset_dev : 0ull);
+  const uint32_t off_lo = static_cast<uint32_t>(offset), off_hi = static_cast<uint32_t>(offset >> 32);
   if (p.dropout) {
     rk = philox_round_keys(p.seed);
 #pragma unroll
