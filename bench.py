@@ -92,10 +92,16 @@ class ClockSampler:
     REASONS = {0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown",
                0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
 
-    def __init__(self, index):
+    def __init__(self, index, enabled=True):
+        # NVML start-up is slow and serialises across processes on a multi-GPU box: construct this BEFORE the
+        # barrier that precedes a timed region (never between the barrier and the first event), and only on the
+        # rank that reports (enabled = rank 0), so that ranks enter the timed loop together.
         self.samples, self.reasons, self.max_mhz = [], set(), None
         self._stop = threading.Event()
         self._t = None
+        self.nv = None
+        if not enabled:
+            return
         try:
             import pynvml
 
@@ -116,7 +122,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(0.002)
+            self._stop.wait(0.004)
 
     def __enter__(self):
         if self.nv is not None:
@@ -271,9 +277,9 @@ def run_point(a, pkg, rank, world, device, with_e2e=True):
     for i in range(a.warmup):
         run_step(i)
     drain()
-    barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(torch.cuda.current_device()) as clk:
+    with ClockSampler(torch.cuda.current_device(), enabled=rank == 0) as clk:
+        barrier()
         e0.record()
         for i in range(a.steps):
             run_step(i)
@@ -343,6 +349,9 @@ def run_point(a, pkg, rank, world, device, with_e2e=True):
             dyd = hdy.to(device, non_blocking=True)
             y = pkg.fused_lora_linear(xd, W, b, Ap, Bp, s, p=p, training=True, w_is_KN=a.conv1d)
             y.backward(dyd)
+            if exch is not None:  # the DDP exchange step, on the gradients autograd produced
+                exch.allreduce_avg_(Ap.grad)
+                exch.allreduce_avg_(Bp.grad)
             hy.copy_(y.detach(), non_blocking=True)
             hdx.copy_(xd.grad, non_blocking=True)
             hda.copy_(Ap.grad, non_blocking=True)
@@ -462,9 +471,9 @@ def run_model(a, pkg, rank, world, device):
     def timed(fn, steps, warmup):
         for i in range(warmup):
             fn(i)
-        barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        with ClockSampler(torch.cuda.current_device()) as clk:
+        with ClockSampler(torch.cuda.current_device(), enabled=rank == 0) as clk:
+            barrier()
             e0.record()
             for i in range(steps):
                 fn(i)
