@@ -8,7 +8,7 @@ echo "pytest exit $?" | tee -a gpurun_out/pytest_gpu.log
 tail -3 gpurun_out/pytest_gpu.log
 timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err
 echo "bench exit $?"; cat gpurun_out/bench.json; tail -5 gpurun_out/bench.err
-SHORT="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
+SHORT="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-graph"
 timeout 300 $SHORT > gpurun_out/plain.log 2>&1 &&
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
     --log-file gpurun_out/launches.csv $SHORT > gpurun_out/ncu_launches.log 2>&1
