@@ -162,6 +162,32 @@ def test_model_with_fast_head_and_loss_matches_stock_path(pkg):
         assert relerr(res[1][1][n], res[0][1][n]) < 5e-2, n
 
 
+def test_disabled_or_merged_adapter_still_backpropagates_to_the_input(pkg):
+    """peft semantics: with adapters disabled (or merged) the layer is the frozen base layer, and dX flows."""
+    torch.manual_seed(0)
+    base = torch.nn.Linear(256, 384).to(torch.bfloat16).cuda()
+    layer = pkg.lora.Linear(base, "default", r=8, lora_alpha=16, lora_dropout=0.0)
+    with torch.no_grad():
+        layer.lora_B["default"].weight.normal_(0, 0.05)
+    x = torch.randn(96, 256, device="cuda", dtype=torch.bfloat16)
+    dy = torch.randn(96, 384, device="cuda", dtype=torch.bfloat16)
+    W, b = base.weight.float().cpu(), base.bias.float().cpu()
+    layer.enable_adapters(False)
+    xg = x.clone().requires_grad_(True)
+    y = layer(xg)
+    y.backward(dy)
+    assert relerr(y, x.float().cpu() @ W.t() + b) < TOL and relerr(xg.grad, dy.float().cpu() @ W) < TOL
+    layer.enable_adapters(True)
+    delta = (layer.lora_B["default"].weight.float() @ layer.lora_A["default"].weight.float()).cpu() * layer.scaling["default"]
+    layer.merge()
+    xg = x.clone().requires_grad_(True)
+    y = layer(xg)
+    y.backward(dy)
+    Wm = W + delta
+    assert relerr(y, x.float().cpu() @ Wm.t() + b) < TOL and relerr(xg.grad, dy.float().cpu() @ Wm) < TOL
+    layer.unmerge()
+
+
 def test_no_cpu_fallback(pkg):
     with pytest.raises(RuntimeError):
         pkg.frozen.fused_causal_lm_loss(torch.zeros(1, 4, 8), torch.zeros(1, 4, dtype=torch.long))

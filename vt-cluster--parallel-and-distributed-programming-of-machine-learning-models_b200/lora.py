@@ -205,10 +205,12 @@ class Linear(nn.Module):
         if self._disable_adapters or self.merged:
             if self._disable_adapters and self.merged:
                 self.unmerge()
-            x2 = x.reshape(-1, x.shape[-1]).to(W.dtype).contiguous()
             if torch.is_grad_enabled() and x.requires_grad:
-                raise RuntimeError("merged / disabled adapters run the inference-only base kernel; "
-                                   "unmerge and enable adapters to train")
+                # gradient w.r.t. the input only (peft: the frozen base layer alone), same tcgen05 GEMM both ways
+                from .frozen import _FrozenLinearFn
+
+                return _FrozenLinearFn.apply(x.to(W.dtype), W, b, int(bool(self.fan_in_fan_out)))
+            x2 = x.reshape(-1, x.shape[-1]).to(W.dtype).contiguous()
             y = binding.linear_base(x2, W, b, self.fan_in_fan_out)
             return y.view(*x.shape[:-1], self.out_features)
         name = self._active_adapter
