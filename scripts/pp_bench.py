@@ -14,6 +14,7 @@ ap.add_argument("--mb", type=int, default=1)
 ap.add_argument("--seq", type=int, default=2048)
 ap.add_argument("--steps", type=int, default=5)
 ap.add_argument("--warmup", type=int, default=2)
+ap.add_argument("--stock-head", action="store_true", help="torch lm_head + fp32 cross-entropy on the last stage")
 a = ap.parse_args()
 g.build()
 pkg = g.load_package()
@@ -32,7 +33,11 @@ full.config.use_cache = False
 pm = pkg.get_peft_model(full, pkg.LoraConfig(r=8, lora_alpha=16, lora_dropout=0.05, bias="none",
                                              target_modules=["q_proj", "k_proj", "v_proj", "out_proj", "fc1", "fc2"],
                                              task_type=pkg.TaskType.CAUSAL_LM))
-stage = pkg.pipeline.OPTStage(pm.base_model.model, rank, world)
+loss_fn = None
+if not a.stock_head:  # lm_head on the tcgen05 GEMM, fused cross-entropy (frozen.py); all six projections are adapters here
+    pkg.frozen.accelerate_lm_head(pm)
+    loss_fn = pkg.frozen.fused_causal_lm_loss
+stage = pkg.pipeline.OPTStage(pm.base_model.model, rank, world, loss_fn=loss_fn)
 stage.to_empty(device=dev)
 gen = torch.Generator(device=dev).manual_seed(1 + rank)
 with torch.no_grad():

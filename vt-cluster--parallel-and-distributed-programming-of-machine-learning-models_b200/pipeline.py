@@ -38,8 +38,11 @@ class OPTStage(nn.Module):
     """Layers [lo, hi) of an OPT decoder, plus the embeddings on the first stage and the
     final LayerNorm / lm_head / loss on the last one."""
 
-    def __init__(self, causal_lm: nn.Module, stage: int, n_stages: int):
+    def __init__(self, causal_lm: nn.Module, stage: int, n_stages: int, loss_fn=None):
         super().__init__()
+        # loss_fn(logits, labels): default torch fp32 shifted cross-entropy; on the GPU pass
+        # frozen.fused_causal_lm_loss (and swap lm_head / frozen neighbours with frozen.accelerate_* first).
+        self.loss_fn = loss_fn
         decoder = causal_lm.model.decoder  # peft_model.base_model.model.model.decoder, :116-118
         counts = split_layers(len(decoder.layers), n_stages)
         lo = sum(counts[:stage])
@@ -90,6 +93,8 @@ class OPTStage(nn.Module):
         if labels is None:
             return logits
         # teacher-forcing next-token loss, finetune_lora_opt_pp.py:147-152
+        if self.loss_fn is not None:
+            return self.loss_fn(logits, labels)
         return F.cross_entropy(logits[:, :-1].contiguous().float().view(-1, logits.size(-1)),
                                labels[:, 1:].contiguous().view(-1), ignore_index=-100)
 
