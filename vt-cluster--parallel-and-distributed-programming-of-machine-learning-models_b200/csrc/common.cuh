@@ -337,6 +337,15 @@ __device__ __forceinline__ uint32_t pack2(float a, float b, int dtype) {
     return *reinterpret_cast<uint32_t*>(&v);
   }
 }
+// Packed FP32 FMA (FFMA2 on sm_100a): two fused multiply-adds per issued instruction.  d = a * b + d, pairwise.
+__device__ __forceinline__ void ffma2(float2& d, const float2 a, const float2 b) {
+  unsigned long long dd = *reinterpret_cast<unsigned long long*>(&d);
+  asm("fma.rn.f32x2 %0, %1, %2, %0;"
+      : "+l"(dd)
+      : "l"(*reinterpret_cast<const unsigned long long*>(&a)), "l"(*reinterpret_cast<const unsigned long long*>(&b)));
+  d = *reinterpret_cast<float2*>(&dd);
+}
+
 __device__ __forceinline__ float2 unpack2(uint32_t w, int dtype) {
   if (dtype == kDtypeBf16) {
     return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&w));

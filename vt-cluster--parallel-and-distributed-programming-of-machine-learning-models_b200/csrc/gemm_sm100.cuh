@@ -139,12 +139,15 @@ __device__ __forceinline__ void cluster_sync_all() {
 // epilogue (warp-level MMA + keep-bits) instead of riding the main loop as a K-block.
 // kAct (unmasked only): the epilogue applies relu / gelu_new after the bias and can store the
 // pre-activation as a second output (tmZ); used for the frozen, un-adapted layers next to the path.
-template <bool kMasked, bool kPair, bool kAct = false>
+// kFma (masked only): padded rank 16 -- the rank-r term runs on the CUDA cores; its own instantiation so that the
+// warp-MMA path's fragments (64+ registers) do not count against it.
+template <bool kMasked, bool kPair, bool kAct = false, bool kFma = false>
 __global__ void __launch_bounds__(THREADS, 1)
     gemm_lora_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                      const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
                      const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmZ, const Params p) {
   static_assert(!(kMasked && kAct), "the activation epilogue belongs to the unmasked kernel");
+  static_assert(kMasked || !kFma, "kFma selects a masked-epilogue flavour");
   using C = Cfg<kPair, kMasked>;
   constexpr int STAGES = C::STAGES;
   constexpr int STAGE_BYTES = C::STAGE_BYTES;
@@ -330,12 +333,12 @@ __global__ void __launch_bounds__(THREADS, 1)
     // (A^T, rank index contiguous) come from the tile's 256-column slice of a16t, which the four
     // epilogue warps copy into smem once per tile while the main loop runs (one contiguous block of
     // 256*rp*2 bytes); only the widest rank (rp = 64, slice too big) reads them from L2 per chunk.
-    const bool slice_in_smem = kMasked && p.dh_ld == 32;
+    const bool slice_in_smem = kMasked && !kFma && p.dh_ld == 32;
     // Padded rank 16 (every adapter of the reference): the warp-level MMAs would queue behind the
     // UMMA stream on the one tensor pipe, so dH.A is formed on the CUDA cores instead, in a compact
     // runtime loop over the rank: A's 16 x 256 slice as fp32 in smem (row reads are warp-uniform
     // broadcasts), this thread's dH row in a per-warp smem column (scratch + 16 KiB).
-    const bool use_fma = kMasked && p.dh_ld == 16;
+    constexpr bool use_fma = kMasked && kFma;
     const float* fslice = reinterpret_cast<const float*>(mask_scratch);                      // [16 j][256 cols]
     float* dh_col = reinterpret_cast<float*>(mask_scratch + 4 * EPI_BUF_BYTES) + ew * 16 * 32;  // [16 j][32 lanes]
     const uint32_t* aslice = reinterpret_cast<const uint32_t*>(mask_scratch + 4 * EPI_BUF_BYTES);  // [256][rp] 16-bit
@@ -351,8 +354,26 @@ __global__ void __launch_bounds__(THREADS, 1)
       // dH rows of this warp as mma.sync A-fragments (2 m16 blocks x up to 4 k16 steps),
       // fetched while the main loop of this tile is still running.
       uint32_t dh_frag[2][4][4];
+      uint32_t kb8[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};  // kFma: this row's keep-bits for the tile's 8 x 32 columns
       if constexpr (kMasked) {
         if (use_fma) {
+          // requested before the accumulator is ready: an L2 round trip per 32-column chunk inside the epilogue
+          // would sit on the critical path of the CTA's last tile, which nothing overlaps
+          if (row_ok) {
+            const uint8_t* kp0 = p.keep + static_cast<size_t>(row) * keep_ld + ((n_blk * BN) >> 3);
+            const bool fast = ((keep_ld | static_cast<int>(reinterpret_cast<uintptr_t>(p.keep))) & 3) == 0;
+#pragma unroll
+            for (int q8 = 0; q8 < 8; ++q8) {
+              const int c = n_blk * BN + q8 * 32;
+              if (fast && c + 32 <= p.N) {
+                kb8[q8] = __ldg(reinterpret_cast<const uint32_t*>(kp0 + q8 * 4));
+              } else {
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                  if (c + q * 8 < p.N) kb8[q8] |= static_cast<uint32_t>(__ldg(kp0 + q8 * 4 + q)) << (8 * q);
+              }
+            }
+          }
           asm volatile("bar.sync 2, 128;" ::: "memory");  // every warp is done with the previous tile's slice
           const int t128 = ew * 32 + lane;
 #pragma unroll
@@ -579,7 +600,8 @@ __global__ void __launch_bounds__(THREADS, 1)
           tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + buf * BN + cb * 64 + h * 32, v);
           const int c = col0 + h * 32;
           uint32_t kbits = 0;
-          if constexpr (kMasked) {
+          if constexpr (kMasked && kFma) kbits = kb8[h];  // rotated by two per 64-column group (static indices only)
+          if constexpr (kMasked && !kFma) {
             // keep-bits of this thread's row for the 32 columns: requested now, consumed after the MMA
             if (row_ok) {
               const uint8_t* kp = p.keep + static_cast<size_t>(row) * keep_ld + (c >> 3);
@@ -663,27 +685,32 @@ __global__ void __launch_bounds__(THREADS, 1)
             }
           }
           if constexpr (kMasked) if (use_fma) {
-            // low[i] = sum_j dH'[row, j] * A[j, c + i]
-            float low[32];
+            // low[i] = sum_j dH'[row, j] * A[j, c + i], as packed FP32 pairs (FFMA2).  Measured on the headline
+            // shape (scripts/masked_probe.py): the kernel pays ~1.45 us per rank iteration of this loop with scalar
+            // FFMA, ~1.2 us with FFMA2, whatever the unroll factor; halving the LDS count (16-bit slice, widened in
+            // registers) made it worse and yielding (nanosleep) inside the loop did not help -- the cost follows the
+            // number of instructions the epilogue warps issue while the main loop of the next tile runs.
+            float2 low2[16];
 #pragma unroll
-            for (int i = 0; i < 32; ++i) low[i] = 0.f;
+            for (int i = 0; i < 16; ++i) low2[i] = make_float2(0.f, 0.f);
             const float* Ac = fslice + cb * 64 + h * 32;
 #pragma unroll 2
             for (int j = 0; j < p.masked_r; ++j) {
               const float d = dh_col[j * 32 + lane];
+              const float2 d2 = make_float2(d, d);
               const float4* Ar = reinterpret_cast<const float4*>(Ac + j * BN);
 #pragma unroll
               for (int q = 0; q < 8; ++q) {
-                const float4 a4 = Ar[q];
-                low[q * 4 + 0] = fmaf(d, a4.x, low[q * 4 + 0]);
-                low[q * 4 + 1] = fmaf(d, a4.y, low[q * 4 + 1]);
-                low[q * 4 + 2] = fmaf(d, a4.z, low[q * 4 + 2]);
-                low[q * 4 + 3] = fmaf(d, a4.w, low[q * 4 + 3]);
+                const float4 a4 = Ar[q];  // warp-uniform address: a broadcast read
+                ffma2(low2[q * 2 + 0], d2, make_float2(a4.x, a4.y));
+                ffma2(low2[q * 2 + 1], d2, make_float2(a4.z, a4.w));
               }
             }
 #pragma unroll
-            for (int i = 0; i < 32; ++i)
-              if ((kbits >> i) & 1u) v[i] = __float_as_uint(__uint_as_float(v[i]) + low[i]);
+            for (int i = 0; i < 16; ++i) {
+              if ((kbits >> (2 * i)) & 1u) v[2 * i] = __float_as_uint(__uint_as_float(v[2 * i]) + low2[i].x);
+              if ((kbits >> (2 * i + 1)) & 1u) v[2 * i + 1] = __float_as_uint(__uint_as_float(v[2 * i + 1]) + low2[i].y);
+            }
           }
           if constexpr (kMasked) if (!use_fma) {
 #pragma unroll
@@ -707,6 +734,10 @@ __global__ void __launch_bounds__(THREADS, 1)
             const int chunk = h * 4 + q;
             *reinterpret_cast<uint4*>(sdst + ((chunk ^ (lane & 7)) << 4)) = o;
           }
+        }
+        if constexpr (kMasked && kFma) {
+#pragma unroll
+          for (int i = 0; i < 6; ++i) kb8[i] = kb8[i + 2];
         }
         fence_proxy_async_smem();
         __syncwarp();

@@ -138,6 +138,8 @@ int device_setup(int* sm_count) {
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<true, false>, gemm::SMEM_BYTES));
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false, true>, gemm::SMEM_BYTES));
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<true, true>, gemm::SMEM_BYTES));
+    CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<true, false, false, true>, gemm::SMEM_BYTES));
+    CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<true, true, false, true>, gemm::SMEM_BYTES));
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false, false, true>, gemm::SMEM_BYTES));
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false, true, true>, gemm::SMEM_BYTES));
 #define OPT_IN_SKINNY(BF, RP)                                                                     \
@@ -368,10 +370,10 @@ bool pair_mode_allowed() {
   return allowed;
 }
 
-template <bool kMasked, bool kPair, bool kAct = false>
+template <bool kMasked, bool kPair, bool kAct = false, bool kFma = false>
 int launch_gemm_t(const CUtensorMap& tmA1, const CUtensorMap& tmB1, const CUtensorMap& tmA2, const CUtensorMap& tmB2,
                   const CUtensorMap& tmD, const CUtensorMap& tmZ, const gemm::Params& p, int grid, cudaStream_t stream) {
-  CUDA_TRY(launch_pdl(gemm::gemm_lora_kernel<kMasked, kPair, kAct>, dim3(grid), dim3(gemm::THREADS), gemm::SMEM_BYTES,
+  CUDA_TRY(launch_pdl(gemm::gemm_lora_kernel<kMasked, kPair, kAct, kFma>, dim3(grid), dim3(gemm::THREADS), gemm::SMEM_BYTES,
                       stream, kPair ? 2 : 1, tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p));
   return 0;
 }
@@ -420,14 +422,23 @@ int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, 
   const long long tiles = ((M + tile_m - 1) / tile_m) * ((N + gemm::BN - 1) / gemm::BN);
   const bool masked = p.masked_r > 0;
   if (masked && p.act) return fail("internal: activation epilogue with the masked kernel");
+  // Timing experiments only (results are wrong): LORA_B200_DEBUG_MASKED_R=j runs the masked kernel with the
+  // rank-r loop cut to j iterations, to separate the loop's cost from the rest of the masked epilogue.
+  static const int dbg_r = [] {
+    const char* e = std::getenv("LORA_B200_DEBUG_MASKED_R");
+    return e ? std::atoi(e) : -1;
+  }();
+  if (masked && dbg_r >= 0) p.masked_r = dbg_r;
   if (pair) {
     const int grid = 2 * static_cast<int>(std::min<long long>(tiles, sm_count / 2));
     if (p.act) return launch_gemm_t<false, true, true>(tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p, grid, stream);
+    if (masked && p.dh_ld == 16) return launch_gemm_t<true, true, false, true>(tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p, grid, stream);
     return masked ? launch_gemm_t<true, true>(tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p, grid, stream)
                   : launch_gemm_t<false, true>(tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p, grid, stream);
   }
   const int grid = static_cast<int>(std::min<long long>(tiles, sm_count));
   if (p.act) return launch_gemm_t<false, false, true>(tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p, grid, stream);
+  if (masked && p.dh_ld == 16) return launch_gemm_t<true, false, false, true>(tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p, grid, stream);
   return masked ? launch_gemm_t<true, false>(tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p, grid, stream)
                 : launch_gemm_t<false, false>(tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p, grid, stream);
 }
