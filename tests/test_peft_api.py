@@ -99,6 +99,22 @@ def test_save_pretrained_layout_and_roundtrip(pkg, tmp_path):
     assert torch.equal(a, b)
 
 
+def test_save_run_writes_adapter_and_run_meta(pkg, tmp_path):
+    """finetune_lora_distilgpt2.py:162-185: rank-0 save of adapter (+ tokenizer) and run_meta.json."""
+    pm = pkg.get_peft_model(_tiny_gpt2(), pkg.LoraConfig(r=8, target_modules=["c_attn"], task_type=pkg.TaskType.CAUSAL_LM))
+    pkg.frozen.accelerate_lm_head(pm)  # the optional module surgery must not change what is saved
+    meta = {"base_model": "distilgpt2", "world_size": 1, "seq_len": 128, "batch": 4, "accum": 32, "lr": 5e-5,
+            "train_seconds": 1.5}
+    out = str(tmp_path / "run")
+    pkg.train.save_run(pm, out, meta)
+    assert json.load(open(os.path.join(out, "run_meta.json"))) == meta
+    assert os.path.exists(os.path.join(out, "adapter_config.json"))
+    from safetensors.torch import load_file
+
+    sd = load_file(os.path.join(out, "adapter_model.safetensors"))
+    assert len(sd) == 12 and all(".lora_A.weight" in k or ".lora_B.weight" in k for k in sd)
+
+
 def test_peft_shim_import(pkg):
     """`from peft import LoraConfig, get_peft_model, TaskType` (finetune_lora_distilgpt2.py:78)
     resolves to this library once <package>/peft_shim is on sys.path."""

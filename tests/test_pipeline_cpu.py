@@ -66,6 +66,8 @@ def _worker(rank, world, port, out_dir, n_layers, n_micro):
     owned = [n for n, p in stage.named_parameters() if p.requires_grad]
     torch.save({"losses": losses, "sd": sd, "owned": owned, "norm": float(eng.last_grad_norm)},
                os.path.join(out_dir, f"rank{rank}.pt"))
+    cfg = pkg.LoraConfig(r=4, lora_alpha=8, target_modules=TARGETS, task_type=pkg.TaskType.CAUSAL_LM)
+    pkg.pipeline.save_adapters(stage, os.path.join(out_dir, "adapters"), peft_config=cfg)  # finetune_lora_opt_pp.py:226-243
     dist.barrier()
     dist.destroy_process_group()
 
@@ -111,3 +113,16 @@ def test_pipeline_equals_unsplit_model(tmp_path, pkg, world, n_layers, n_micro):
             assert torch.allclose(r["sd"][gname], ref_sd[gname], rtol=1e-4, atol=1e-6), gname
             seen.add(gname)
     assert seen == {n for n, p in pm.named_parameters() if p.requires_grad}
+    # rank 0 wrote ONE peft-format directory holding every stage's adapters
+    import json
+
+    from safetensors.torch import load_file
+
+    saved = load_file(str(tmp_path / "adapters" / "adapter_model.safetensors"))
+    want = {n.replace(".default.", "."): p for n, p in pm.named_parameters() if p.requires_grad}
+    assert set(saved) == set(want)
+    for k, v in saved.items():
+        assert torch.allclose(v, want[k].detach(), rtol=1e-4, atol=1e-6), k
+    meta = json.load(open(tmp_path / "adapters" / "meta.json"))
+    assert meta == {"split": counts, "stages": world}
+    assert json.load(open(tmp_path / "adapters" / "adapter_config.json"))["r"] == 4

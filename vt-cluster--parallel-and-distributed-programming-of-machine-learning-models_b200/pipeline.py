@@ -229,3 +229,54 @@ class PipelineEngine:
     def zero_grad(self):
         if self.opt is not None:
             self.opt.zero_grad(set_to_none=True)
+
+
+def save_adapters(stage: OPTStage, save_dir: str, peft_config=None, meta: Optional[dict] = None,
+                  adapter_name: str = "default", group=None) -> None:
+    """Adapter save for a pipeline run (finetune_lora_opt_pp.py:226-243: rank 0 writes the adapters and
+    meta.json with the split).  Every adapter lives on exactly one stage, so each rank hands its own
+    tensors -- renamed from the stage's local `layers.<i>` to the peft key of the unsplit model -- to
+    rank 0, which writes ONE peft-format directory: adapter_model.safetensors, adapter_config.json (when
+    the LoraConfig is given) and meta.json."""
+    import json
+    import os
+
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    n_layers = stage.config.num_hidden_layers
+    counts = split_layers(n_layers, stage.n_stages)
+    lo = sum(counts[:stage.stage])
+    mine = {}
+    for name, prm in stage.named_parameters():
+        if "lora_" not in name or f".{adapter_name}." not in name:
+            continue
+        local, rest = name.split(".", 2)[1:]
+        key = f"base_model.model.model.decoder.layers.{lo + int(local)}.{rest}".replace(f".{adapter_name}.", ".")
+        mine[key] = prm.detach().to("cpu", torch.float32).contiguous()
+    shards = [None] * world
+    if world > 1:
+        dist.gather_object(mine, shards if rank == 0 else None, dst=0, group=group)
+    else:
+        shards = [mine]
+    if rank == 0:
+        merged = {}
+        for s in shards:
+            dup = set(merged) & set(s)
+            if dup:
+                raise RuntimeError(f"adapter tensors owned by two stages: {sorted(dup)[:3]}")
+            merged.update(s)
+        os.makedirs(save_dir, exist_ok=True)
+        from safetensors.torch import save_file
+
+        save_file(merged, os.path.join(save_dir, "adapter_model.safetensors"), metadata={"format": "pt"})
+        if peft_config is not None:
+            cfg = peft_config.to_dict()
+            cfg["inference_mode"] = True
+            with open(os.path.join(save_dir, "adapter_config.json"), "w") as f:
+                json.dump(cfg, f, indent=2, sort_keys=True)
+        m = {"split": counts, "stages": stage.n_stages}
+        m.update(meta or {})
+        with open(os.path.join(save_dir, "meta.json"), "w") as f:
+            json.dump(m, f, indent=2)
+    if world > 1:
+        dist.barrier(group=group)

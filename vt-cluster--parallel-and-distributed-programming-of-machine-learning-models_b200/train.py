@@ -150,6 +150,28 @@ class Trainer:
         return losses
 
 
+def save_run(model: nn.Module, save_dir: str, meta: Optional[Dict] = None, tokenizer=None,
+             meta_name: str = "run_meta.json") -> None:
+    """Rank-0-only adapter save between two barriers, as finetune_lora_distilgpt2.py:162-189 does it:
+    `save_pretrained` (adapter_config.json + adapter_model.safetensors), the tokenizer when given, and the
+    run's metadata (base model, world size, seq_len, batch, accum, lr, train_seconds, ...) as JSON."""
+    import json
+
+    on = dist.is_available() and dist.is_initialized()
+    if on:
+        dist.barrier()
+    if not on or dist.get_rank() == 0:
+        core = model.module if hasattr(model, "module") and hasattr(model.module, "save_pretrained") else model
+        core.save_pretrained(save_dir)
+        if tokenizer is not None:
+            tokenizer.save_pretrained(save_dir)
+        if meta is not None:
+            with open(os.path.join(save_dir, meta_name), "w") as f:
+                json.dump(meta, f, indent=2)
+    if on:
+        dist.barrier()
+
+
 def init_distributed(backend: Optional[str] = None):
     """env:// rendezvous as in finetune_lora_distilgpt2.py:35-45, NCCL on GPUs (gloo only in the
     CPU tests).  Returns (rank, world, local_rank)."""
