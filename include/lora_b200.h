@@ -205,6 +205,15 @@ int lora_bucket_allreduce_avg(float* bucket, int64_t n, void* const* syms, int32
                               int64_t capacity_floats, int32_t mode, cudaStream_t stream);
 
 /*
+ * Merge / unmerge of one adapter into its frozen 16-bit weight, in place (peft's
+ * lora.Linear.merge()/unmerge(), reached after training through merge_and_unload-style use of the adapters the
+ * reference saves at finetune_lora_distilgpt2.py:167): W <- W + scale * B A, scale = +lora_alpha/r to merge,
+ * -lora_alpha/r to unmerge.  W is [N, K], or [K, N] with w_is_KN; A [r, K], B [N, r] fp32.
+ */
+int lora_merge_weight(void* W, const float* A, const float* B, int64_t K, int64_t N, int32_t r, float scale, int32_t dtype,
+                      int32_t w_is_KN, cudaStream_t stream);
+
+/*
  * Token cross-entropy from 16-bit logits; replaces the fp32 logits copy +
  * log_softmax + nll_loss that the HF causal-LM loss runs on DataCollatorForLanguageModeling labels
  * (finetune_lora_distilgpt2.py:114) and nn.CrossEntropyLoss in finetune_lora_opt_pp.py:143-153.

@@ -188,6 +188,34 @@ def test_disabled_or_merged_adapter_still_backpropagates_to_the_input(pkg):
     layer.unmerge()
 
 
+@pytest.mark.parametrize("conv1d,dtype", [(False, torch.bfloat16), (True, torch.bfloat16), (True, torch.float16)])
+def test_merge_kernel_both_layouts(pkg, conv1d, dtype):
+    """W <- W + s B A in place (row N4): against the fp32 sum rounded once; unmerge returns W up to one rounding."""
+    from transformers.pytorch_utils import Conv1D
+
+    K, N, r = 264, 520, 8
+    torch.manual_seed(3)
+    base = (Conv1D(N, K) if conv1d else torch.nn.Linear(K, N)).to(dtype).cuda()
+    with torch.no_grad():
+        base.weight.normal_(0, 0.05)
+    layer = pkg.lora.Linear(base, "default", r=r, lora_alpha=16, lora_dropout=0.0, fan_in_fan_out=conv1d)
+    with torch.no_grad():
+        layer.lora_B["default"].weight.normal_(0, 0.05)
+    w0 = base.weight.detach().clone()
+    delta = (layer.lora_B["default"].weight.float() @ layer.lora_A["default"].weight.float()) * layer.scaling["default"]
+    if conv1d:
+        delta = delta.t()
+    layer.merge()
+    want = (w0.float() + delta).to(dtype)
+    ulp = 2.0 ** (-8 if dtype == torch.bfloat16 else -11)
+    got = base.weight.detach()
+    # fp32 product and sum, one rounding: equal to the reference except where fp32 summation order flips a rounding
+    assert float((got != want).float().mean()) < 1e-3
+    assert float((got.float() - want.float()).abs().max()) <= ulp * float(want.float().abs().max())
+    layer.unmerge()
+    assert float((base.weight.detach().float() - w0.float()).abs().max()) <= 2 * ulp * float(want.float().abs().max())
+
+
 def test_no_cpu_fallback(pkg):
     with pytest.raises(RuntimeError):
         pkg.frozen.fused_causal_lm_loss(torch.zeros(1, 4, 8), torch.zeros(1, 4, dtype=torch.long))

@@ -55,6 +55,7 @@ _SIGNATURES = {
     "lora_p2p_free": (c_int, [c_void_p]),
     "lora_bucket_allreduce_avg": (c_int, [c_void_p, c_int64, ctypes.POINTER(c_void_p), c_int32, c_int32, c_int64, c_int32,
                                           c_void_p]),
+    "lora_merge_weight": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int32, c_float, c_int32, c_int32, c_void_p]),
     "lora_ce_fwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int32, c_void_p]),
     "lora_ce_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64,
                             c_int32, c_void_p]),

@@ -706,6 +706,24 @@ int lora_act_bwd(const void* dY, const void* ZorY, void* dZ, int64_t n_elems, in
   return 0;
 }
 
+int lora_merge_weight(void* W, const float* A, const float* B, int64_t K, int64_t N, int32_t r, float scale, int32_t dtype,
+                      int32_t w_is_KN, cudaStream_t stream) {
+  g_err.clear();
+  if (!W || !A || !B) return fail("lora_merge_weight: null pointer argument");
+  if (K <= 0 || N <= 0 || r < 1 || r > 64) return fail("lora_merge_weight: need K, N > 0 and 1 <= r <= 64");
+  if (dtype != kDtypeBf16 && dtype != kDtypeFp16) return fail("dtype must be 0 (bf16) or 1 (fp16); fp32 is not supported");
+  if ((w_is_KN ? N : K) % 8) return fail("lora_merge_weight: the weight's row length (%s) must be a multiple of 8", w_is_KN ? "N" : "K");
+  if ((reinterpret_cast<uintptr_t>(W) | reinterpret_cast<uintptr_t>(A)) & 15) return fail("lora_merge_weight: W and A must be 16-byte aligned");
+  int sms = 0;
+  if (device_setup(&sms)) return 1;
+  const long long groups = static_cast<long long>(K) * N / 8;
+  const int grid = static_cast<int>(std::max<long long>(1, std::min<long long>((groups + act::THREADS - 1) / act::THREADS, 16LL * sms)));
+  act::merge_kernel<<<grid, act::THREADS, 0, stream>>>(static_cast<uint16_t*>(W), A, B, (long long)N, (long long)K, (int)r, scale,
+                                                     (int)w_is_KN, (int)dtype);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
 int lora_frozen_linear_bwd(const void* dY, int64_t lddy, const void* W, void* dX, int64_t lddx, int64_t M, int64_t K,
                            int64_t N, int32_t dtype, int32_t w_is_KN, cudaStream_t stream) {
   g_err.clear();

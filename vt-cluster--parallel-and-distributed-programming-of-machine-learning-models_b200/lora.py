@@ -187,16 +187,31 @@ class Linear(nn.Module):
         for name in adapter_names or self.active_adapters:
             if name in self.merged_adapters:
                 continue
-            delta = self.get_delta_weight(name)
-            if safe_merge and not torch.isfinite(delta).all():
+            if safe_merge and not torch.isfinite(self.get_delta_weight(name)).all():
                 raise ValueError(f"NaNs detected in the merged weights of adapter {name}")
-            self.base_layer.weight.data += delta
+            self._add_delta(name, +1.0)
             self.merged_adapters.append(name)
 
     def unmerge(self):
         while self.merged_adapters:
-            name = self.merged_adapters.pop()
-            self.base_layer.weight.data -= self.get_delta_weight(name)
+            self._add_delta(self.merged_adapters.pop(), -1.0)
+
+    def _add_delta(self, name: str, sign: float):
+        """W += sign * s * B A.  16-bit CUDA weights: the in-place kernel (fp32 product, one rounding);
+        anything else (fp32 / CPU set-up code and the CPU unit tests): plain torch."""
+        W = self.base_layer.weight
+        A, B = self.lora_A[name].weight, self.lora_B[name].weight
+        if W.is_cuda and W.dtype in (torch.bfloat16, torch.float16) and W.is_contiguous():
+            import ctypes
+
+            rc = binding.lib().lora_merge_weight(
+                ctypes.c_void_p(W.data_ptr()), ctypes.c_void_p(A.detach().float().contiguous().data_ptr()),
+                ctypes.c_void_p(B.detach().float().contiguous().data_ptr()), self.in_features, self.out_features,
+                A.shape[0], float(sign * self.scaling[name]), binding.dtype_code(W.dtype), int(bool(self.fan_in_fan_out)),
+                ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+            binding._check(rc, "lora_merge_weight")
+        else:
+            W.data += sign * self.get_delta_weight(name)
 
     # ---- forward -------------------------------------------------------------------
     def forward(self, x: torch.Tensor) -> torch.Tensor:
