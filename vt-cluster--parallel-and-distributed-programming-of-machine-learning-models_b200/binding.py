@@ -86,6 +86,10 @@ def lib() -> ctypes.CDLL:
     return _lib
 
 
+def last_error() -> str:
+    return lib().lora_last_error().decode()
+
+
 def _check(rc: int, what: str):
     if rc != 0:
         raise RuntimeError(f"{what}: {lib().lora_last_error().decode()}")

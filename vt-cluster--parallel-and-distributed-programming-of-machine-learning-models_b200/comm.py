@@ -35,22 +35,40 @@ class PeerBucketExchange:
             raise RuntimeError(f"PeerBucketExchange spans one box: at most {MAX_WORLD} ranks, got {self.world}")
         self.capacity = int(capacity_floats)
         self._lib = binding.lib()
+        # Set-up is collective and must fail on ALL ranks or on none: local steps record their error, the
+        # collectives that follow always run, and everybody learns whether anybody failed.
         self._own = ctypes.c_void_p()
-        handle = ctypes.create_string_buffer(64)
-        binding._check(self._lib.lora_p2p_alloc(self.capacity, ctypes.byref(self._own), handle), "lora_p2p_alloc")
-        handles = [None] * self.world
-        dist.all_gather_object(handles, handle.raw, group=group)
-        self._syms = (ctypes.c_void_p * self.world)()
         self._opened = []
-        for q in range(self.world):
-            if q == self.rank:
-                self._syms[q] = self._own
-            else:
+        handle = ctypes.create_string_buffer(64)
+        err = None
+        if self._lib.lora_p2p_alloc(self.capacity, ctypes.byref(self._own), handle) != 0:
+            err = "lora_p2p_alloc: " + binding.last_error()
+            self._own = None
+        handles = [None] * self.world
+        dist.all_gather_object(handles, handle.raw if err is None else None, group=group)
+        self._syms = (ctypes.c_void_p * self.world)()
+        if err is None and all(h is not None for h in handles):
+            for q in range(self.world):
+                if q == self.rank:
+                    self._syms[q] = self._own
+                    continue
                 peer = ctypes.c_void_p()
-                binding._check(self._lib.lora_p2p_open(handles[q], ctypes.byref(peer)), "lora_p2p_open")
+                if self._lib.lora_p2p_open(handles[q], ctypes.byref(peer)) != 0:
+                    err = f"lora_p2p_open(rank {q}): " + binding.last_error()
+                    break
                 self._syms[q] = peer
                 self._opened.append(peer)
-        dist.barrier(group=group)  # nobody frees or reuses anything before everybody has mapped everything
+        elif err is None:
+            err = "a peer rank could not allocate its exchange buffer"
+        ok = torch.tensor([1 if err is None else 0], device="cuda", dtype=torch.int32)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)  # also: nobody proceeds before everybody has mapped
+        if int(ok.item()) == 0:
+            for p in self._opened:
+                self._lib.lora_p2p_close(p)
+            if self._own is not None:
+                self._lib.lora_p2p_free(self._own)
+            self._own, self._opened = None, []
+            raise RuntimeError("peer-memory exchange set-up failed: " + (err or "on another rank"))
 
     def allreduce_avg_(self, t: torch.Tensor, mode: int = 0) -> torch.Tensor:
         """t <- mean over ranks, in place, enqueued on the current stream (fp32, contiguous, CUDA)."""
@@ -79,3 +97,15 @@ class PeerBucketExchange:
             self._lib.lora_p2p_close(p)
         self._lib.lora_p2p_free(self._own)
         self._own, self._opened = None, []
+
+
+def try_peer_exchange(capacity_floats: int, group: Optional[dist.ProcessGroup] = None) -> Optional[PeerBucketExchange]:
+    """PeerBucketExchange if EVERY rank could set it up (CUDA IPC allowed, peers P2P-capable), else None on every
+    rank -- the caller then keeps the NCCL all-reduce.  Set-up fails collectively, so ranks cannot diverge."""
+    import sys
+
+    try:
+        return PeerBucketExchange(capacity_floats, group)
+    except RuntimeError as e:
+        print(f"[lora_b200] rank {dist.get_rank(group) if dist.is_initialized() else 0}: {e}; using NCCL", file=sys.stderr)
+        return None

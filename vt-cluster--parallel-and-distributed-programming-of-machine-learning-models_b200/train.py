@@ -77,11 +77,12 @@ def wrap_ddp(model: nn.Module, device: Optional[torch.device] = None, bucket_cap
     if device is not None and device.type == "cuda":
         ddp = DDP(model, device_ids=[device.index], output_device=device.index, **kw)
         if exchange == "p2p":
-            from .comm import PeerBucketExchange
+            from .comm import try_peer_exchange
 
             n = sum(p.numel() for p in model.parameters() if p.requires_grad)
-            ddp._lora_exchange = PeerBucketExchange(n)  # kept alive with the wrapper
-            ddp.register_comm_hook(None, ddp._lora_exchange.ddp_hook)
+            ddp._lora_exchange = try_peer_exchange(n)  # kept alive with the wrapper; None: NCCL stays
+            if ddp._lora_exchange is not None:
+                ddp.register_comm_hook(None, ddp._lora_exchange.ddp_hook)
         return ddp
     if exchange == "p2p":
         raise RuntimeError("exchange='p2p' needs CUDA devices (no CPU fallback)")
