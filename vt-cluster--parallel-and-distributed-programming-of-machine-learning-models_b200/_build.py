@@ -22,20 +22,35 @@ def _stale() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile csrc/*.cu -> liblora_b200.so (sm_100a only).  Returns the library path."""
+    """Compile csrc/*.cu -> liblora_b200.so (sm_100a only).  Returns the library path.
+    Safe when several ranks of one job call it at once: an exclusive file lock serialises the staleness check and
+    the compile, and the library is written under a temporary name and renamed into place."""
     if not force and not _stale():
         return LIB_PATH
-    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
-    cmd = [
-        nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-        "-shared", "-Xcompiler", "-fPIC", "-I", os.path.join(REPO_ROOT, "include"), "-I", CSRC,
-        "-o", LIB_PATH,
-    ] + [os.path.join(CSRC, s) for s in SOURCES]
-    if verbose:
-        cmd.insert(1, "-Xptxas=-v")
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
-    if verbose:
-        print(res.stderr)
+    import fcntl
+
+    with open(LIB_PATH + ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not _stale():  # another rank built it while this one waited
+                return LIB_PATH
+            nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+            tmp = f"{LIB_PATH}.tmp{os.getpid()}"
+            cmd = [
+                nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+                "-shared", "-Xcompiler", "-fPIC", "-I", os.path.join(REPO_ROOT, "include"), "-I", CSRC,
+                "-o", tmp,
+            ] + [os.path.join(CSRC, s) for s in SOURCES]
+            if verbose:
+                cmd.insert(1, "-Xptxas=-v")
+            res = subprocess.run(cmd, capture_output=True, text=True)
+            if res.returncode != 0:
+                if os.path.exists(tmp):
+                    os.remove(tmp)
+                raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+            os.replace(tmp, LIB_PATH)
+            if verbose:
+                print(res.stderr)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
     return LIB_PATH
