@@ -171,12 +171,23 @@ def cpu_step_time(a, tokens, steps, warmup):
     return (time.perf_counter() - t0) / steps
 
 
+def use_all_host_threads() -> int:
+    """The CPU arms run on every core this process may use.  torchrun exports OMP_NUM_THREADS=1 to its workers,
+    which would otherwise pin the reference arm of an N > 1 launch to a single thread."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    torch.set_num_threads(max(1, n))
+    return torch.get_num_threads()
+
+
 def run_reference(a, rank):
     """--impl reference: the reference's own CPU implementation of the path.  peft/accelerate/
     deepspeed cannot be installed here, so this is the oracle port on all host threads."""
     if rank != 0:
         return
-    cores = torch.get_num_threads()
+    cores = use_all_host_threads()
     t = cpu_step_time(a, a.cpu_tokens, a.steps, max(1, min(a.warmup, 3)))
     v = a.cpu_tokens / t
     sample = f"{a.cpu_tokens} tokens/step x {a.steps} steps of the same layer shape, torch fp32 CPU"
@@ -511,6 +522,7 @@ def run_reference_model(a, rank):
     bounded 2-layer slice of the same architecture."""
     if rank != 0:
         return
+    use_all_host_threads()
     from oracle import lora_ref
 
     a2 = argparse.Namespace(**vars(a))
@@ -588,7 +600,7 @@ def main():
         line = run_point(a, pkg, rank, world, device)
         if rank == 0:
             if world == 1 and not a.no_cpu_baseline:
-                cores = torch.get_num_threads()
+                cores = use_all_host_threads()
                 t = cpu_step_time(a, a.cpu_tokens, 5, 1)
                 line["cpu_baseline"] = {"value": a.cpu_tokens / t, "unit": UNIT, "cores": cores, "kind": "port",
                                         "sample": f"{a.cpu_tokens} tokens/step x 5 steps, same layer shape, "
