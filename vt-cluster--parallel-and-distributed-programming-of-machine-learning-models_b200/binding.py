@@ -7,6 +7,7 @@ shared library is missing or fails to load, importing the product fails loudly.
 from __future__ import annotations
 
 import ctypes
+import functools
 import os
 from ctypes import c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_uint32, c_uint64, c_void_p
 
@@ -107,7 +108,14 @@ def _ptr(t):
     return None if t is None else t.data_ptr()
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def _stream() -> int:
+    """cudaStream_t of torch's current stream on the current device (the raw getter skips building a Stream object:
+    this sits on the per-layer launch path, which bounds the small models' step time)."""
+    if _raw_stream is not None:
+        return _raw_stream(torch.cuda.current_device())
     return torch.cuda.current_stream().cuda_stream
 
 
@@ -117,10 +125,12 @@ def _need_cuda(*ts):
             raise RuntimeError("fused LoRA kernels need contiguous CUDA tensors (no CPU fallback)")
 
 
+@functools.lru_cache(maxsize=None)
 def rpad(r: int) -> int:
     return int(lib().lora_linear_rpad(int(r)))
 
 
+@functools.lru_cache(maxsize=4096)
 def workspace_bytes(M: int, K: int, N: int, r: int) -> int:
     return int(lib().lora_linear_workspace_bytes(M, K, N, r))
 
