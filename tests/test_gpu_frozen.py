@@ -216,6 +216,34 @@ def test_merge_kernel_both_layouts(pkg, conv1d, dtype):
     assert float((base.weight.detach().float() - w0.float()).abs().max()) <= 2 * ulp * float(want.float().abs().max())
 
 
+def test_committed_golden_vectors(pkg):
+    """tests/golden/frozen_golden.npz (oracle/make_golden_frozen.py: transformers Conv1D + NewGELUActivation,
+    nn.Linear + ReLU, shifted F.cross_entropy, all fp32 on the CPU) through the device kernels."""
+    import os
+
+    import numpy as np
+    from transformers.pytorch_utils import Conv1D
+
+    gold = np.load(os.path.join(os.path.dirname(__file__), "golden", "frozen_golden.npz"))
+    T = lambda k: torch.from_numpy(gold[k])
+    for name, act in (("gelu", "gelu_new"), ("relu", "relu")):
+        M, K, N, kn = (int(v) for v in gold[f"{name}_meta"])
+        base = Conv1D(N, K) if kn else torch.nn.Linear(K, N)
+        with torch.no_grad():
+            base.weight.copy_(T(f"{name}_W"))
+            base.bias.copy_(T(f"{name}_b"))
+        fl = pkg.frozen.FrozenLinear(base.to(torch.bfloat16).requires_grad_(False).cuda(), act=act)
+        xg = T(f"{name}_x").to(torch.bfloat16).cuda().requires_grad_(True)
+        y = fl(xg)
+        y.backward(T(f"{name}_dy").to(torch.bfloat16).cuda())
+        assert relerr(y, T(f"{name}_y")) < TOL and relerr(xg.grad, T(f"{name}_dx")) < TOL, name
+    lg = T("ce_logits").to(torch.bfloat16).cuda().requires_grad_(True)
+    loss = pkg.frozen.fused_causal_lm_loss(lg, T("ce_labels").cuda())
+    loss.backward()
+    assert abs(float(loss.detach()) - float(gold["ce_loss"])) / float(gold["ce_loss"]) < 2e-3
+    assert relerr(lg.grad, T("ce_dlogits")) < TOL
+
+
 def test_no_cpu_fallback(pkg):
     with pytest.raises(RuntimeError):
         pkg.frozen.fused_causal_lm_loss(torch.zeros(1, 4, 8), torch.zeros(1, 4, dtype=torch.long))
