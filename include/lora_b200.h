@@ -192,7 +192,7 @@ int lora_act_bwd(const void* dY, const void* ZorY, void* dZ, int64_t n_elems, in
  *                    device) and stream-ordered, no host synchronisation.  Every rank sums in rank order, so all ranks
  *                    get the bit-identical result.  mode 0 picks one-shot (small buckets) or two-shot
  *                    (reduce my slice, push it to every peer) by size.
- * A rank that never calls trips the device watchdog (trap after 2^33 cycles) on its peers.
+ * A rank that never calls trips the device watchdog on its peers (trap after 2^40 cycles, about nine minutes).
  */
 #define LORA_P2P_HANDLE_BYTES 64
 #define LORA_P2P_MAX_WORLD 8

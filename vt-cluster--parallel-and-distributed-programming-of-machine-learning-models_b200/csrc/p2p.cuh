@@ -24,8 +24,8 @@
 // finishing its reads of this call (kernels of one stream run in order).  Flags compare with ==, and a
 // peer cannot publish seq + 2 before this rank has published seq + 1, i.e. has consumed seq.
 //
-// Nothing here allocates or synchronises the host; a peer that never arrives trips the same
-// clock64 watchdog as the mbarrier waits (trap instead of a hung GPU).
+// Nothing here allocates or synchronises the host; a peer that never arrives trips a clock64 watchdog
+// (PEER_WATCHDOG_CYCLES, minutes) and the kernel traps instead of spinning for ever.
 #pragma once
 
 #include "common.cuh"
@@ -37,6 +37,10 @@ constexpr int MAX_WORLD = 8;
 constexpr int THREADS = 512;
 constexpr int MAX_CTAS = 64;  // all CTAs must be co-resident (they wait for each other): far below 148 SMs
 constexpr int CTRL_BYTES = 1024;
+// A collective must tolerate a rank that is late for ordinary reasons (first-iteration library set-up, a slow input
+// pipeline, a garbage-collection pause): the peers' wait gives up only after 2^40 cycles (~9 minutes at 1.96 GHz),
+// far beyond the 2^33 cycles (~4 s) of the intra-kernel mbarrier watchdog.
+constexpr long long PEER_WATCHDOG_CYCLES = 1ll << 40;
 
 struct Ctrl {
   uint32_t flag_a[2][MAX_WORLD];  // [parity][source rank] = seq: source's data[parity] is complete
@@ -93,7 +97,7 @@ __device__ __forceinline__ void publish_and_wait(const Peers& peers, int rank, i
     const long long t0 = clock64();
     uint32_t spins = 0;
     while (ld_acquire_sys(f) != seq) {
-      if (((++spins) & 0x3ffu) == 0 && (clock64() - t0) > LB_WATCHDOG_CYCLES) {
+      if (((++spins) & 0x3ffu) == 0 && (clock64() - t0) > PEER_WATCHDOG_CYCLES) {
         printf("lora_b200: peer rank %d never arrived at exchange %u (round %d); aborting\n", (int)threadIdx.x, seq, round);
         __trap();
       }
