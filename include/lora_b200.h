@@ -44,8 +44,24 @@ const char* lora_last_error(void);
 /* Rank padded to the tensor-core K granule the kernels use: 16, 32 or 64. */
 int32_t lora_linear_rpad(int32_t r);
 
-/* Bytes of caller-owned scratch that lora_linear_fwd / lora_linear_bwd need. */
+/*
+ * Bytes of the packed-operand block of one adapted layer (see lora_linear_fwd): the fp32 adapter
+ * masters A, B as 16-bit tensor-core operands in the four layouts the kernels read.  No
+ * counterpart in the reference (peft casts nothing; torch's CPU GEMMs read fp32).
+ */
+size_t lora_linear_packed_bytes(int64_t K, int64_t N, int32_t r);
+
+/* Bytes of caller-owned scratch that lora_linear_bwd needs (the forward needs none). */
 size_t lora_linear_workspace_bytes(int64_t M, int64_t K, int64_t N, int32_t r);
+
+/*
+ * A [r,K], B [N,r] (fp32 masters) -> packed [lora_linear_packed_bytes], 256-byte aligned.
+ * lora_linear_fwd does this itself when handed A and B; the separate entry point is for callers
+ * that run a backward without a forward of their own, or that pack once per optimiser step and
+ * pass A = B = NULL to the forward.  No counterpart in the reference.
+ */
+int lora_linear_pack(const float* A, const float* B, void* packed, size_t packed_bytes, int64_t K, int64_t N, int32_t r,
+                     float scaling, int32_t dtype, cudaStream_t stream);
 
 /*
  * Forward of one LoRA-adapted projection; replaces peft lora.Linear.forward
@@ -57,15 +73,17 @@ size_t lora_linear_workspace_bytes(int64_t M, int64_t K, int64_t N, int32_t r);
  * p > 0 draws the dropout mask from Philox4x32-10 keyed by (seed, offset) (p is
  * resolved to 1/16384: an element is dropped with probability round(p*16384)/16384) and
  * writes the keep-bits to keep_mask (needed by backward); p == 0 ignores
- * keep_mask (may be NULL).  Xd (optional, [M,K], may be NULL) receives
- * keep .* X -- the tensor torch autograd would save for lora_A's weight
- * gradient -- so that backward need not re-apply the mask; only written
- * when p > 0.
+ * keep_mask (may be NULL).
+ * `packed` (caller-owned, lora_linear_packed_bytes, 256-byte aligned) receives the 16-bit operand
+ * forms of A and B; hand the same block to lora_linear_bwd, which therefore differentiates with the
+ * adapter values the forward saw (what autograd's saved tensors give the reference).  A = B = NULL:
+ * `packed` already holds them (lora_linear_pack).  What the backward needs from the forward is
+ * X itself, H, keep_mask and packed -- no masked copy of X is written.
  */
 int lora_linear_fwd(const void* X, const void* W, const void* bias, const float* A, const float* B, void* Y, void* H,
-                    uint8_t* keep_mask, void* Xd, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p,
-                    uint64_t seed, uint64_t offset, int32_t dtype, int32_t w_is_KN, void* workspace,
-                    size_t workspace_bytes, cudaStream_t stream);
+                    uint8_t* keep_mask, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p, uint64_t seed,
+                    uint64_t offset, int32_t dtype, int32_t w_is_KN, void* packed, size_t packed_bytes,
+                    cudaStream_t stream);
 
 /*
  * lora_linear_fwd whose dropout offset also has a device-side part: the Philox offset used is
@@ -75,9 +93,9 @@ int lora_linear_fwd(const void* X, const void* W, const void* bias, const float*
  * (the reference's lora_dropout is torch.nn.Dropout inside peft's lora.Linear).  No other difference.
  */
 int lora_linear_fwd_devrng(const void* X, const void* W, const void* bias, const float* A, const float* B, void* Y, void* H,
-                           uint8_t* keep_mask, void* Xd, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p,
+                           uint8_t* keep_mask, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p,
                            uint64_t seed, uint64_t offset, const uint64_t* offset_dev, int32_t dtype, int32_t w_is_KN,
-                           void* workspace, size_t workspace_bytes, cudaStream_t stream);
+                           void* packed, size_t packed_bytes, cudaStream_t stream);
 
 /*
  * Backward of the same projection; replaces what torch autograd derives from
@@ -86,13 +104,14 @@ int lora_linear_fwd_devrng(const void* X, const void* W, const void* bias, const
  *     dB = scaling * dY^T H               dA = dH^T dropout_p(X)
  * No dW, no dbias (base layer frozen, LoraConfig bias="none").  dX may be NULL
  * (input needs no gradient).  dA [r,K] and dB [N,r] are fp32 and are
- * overwritten, or added to when accumulate != 0.  X is the forward input, or,
- * with x_is_dropped != 0, the Xd tensor forward wrote (keep .* X).
+ * overwritten, or added to when accumulate != 0.  X is the forward's input (the mask is re-applied
+ * from keep_mask), `packed` the block the forward (or lora_linear_pack) filled, `workspace` scratch of
+ * lora_linear_workspace_bytes that must not be shared by calls that may overlap on the GPU.
  */
-int lora_linear_bwd(const void* dY, const void* X, const void* W, const float* A, const float* B, const void* H,
+int lora_linear_bwd(const void* dY, const void* X, const void* W, const void* packed, const void* H,
                     const uint8_t* keep_mask, void* dX, float* dA, float* dB, int64_t M, int64_t K, int64_t N,
                     int32_t r, float scaling, float p, int32_t dtype, int32_t w_is_KN, int32_t accumulate,
-                    int32_t x_is_dropped, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+                    void* workspace, size_t workspace_bytes, cudaStream_t stream);
 
 /*
  * Frozen projection alone, Y = X W^T + bias: the base_layer call of peft's
@@ -118,7 +137,7 @@ int lora_dropout_keep_mask(uint8_t* keep_mask, int64_t M, int64_t K, float p, ui
  * example a plug-in hosted by a runtime whose own pool already owns the GPU's memory (a cudaMalloc
  * from inside the plug-in may fail, or fragment that pool), or a latency-sensitive loop that must
  * not hit the driver's allocator (cudaMalloc / cudaFree synchronise the device).  This entry point
- * calls no cudaMalloc, cudaFree or other allocating routine.  The split partial sums that
+ * calls no cudaMalloc, cudaFree or other allocating routine (see the note on the first call below).  The split partial sums that
  * lora_linear_bwd keeps in the caller's workspace live here in a block of
  * LORA_B200_STATIC_SCRATCH_BYTES that is compiled into the library (every GPU that loads the
  * library holds it until the process exits).  The caller still passes the inputs dY [M,N] and
@@ -128,9 +147,11 @@ int lora_dropout_keep_mask(uint8_t* keep_mask, int64_t M, int64_t K, float p, ui
  *  - Shapes whose partial sums do not fit the block are rejected with an error message that
  *    states the need and the limit (roughly: row-splits * N * padded-rank * 4 bytes; all the
  *    reference's shapes at r <= 16 fit).  Use lora_linear_bwd for those.
- *  - The first call on each device looks up the block's device address (one
- *    cudaGetSymbolAddress, no allocation); make that first call before starting any stream
- *    capture on that device.
+ *  - No allocation after the first call on a device.  That first call does the library's one-time
+ *    set-up for the device: kernel attributes (cudaFuncSetAttribute), the block's device address
+ *    (one cudaGetSymbolAddress) and, under CUDA's lazy loading, the module load during which the
+ *    driver reserves the block itself.  Make it at start-up, before any stream capture on that
+ *    device and outside any region in which the allocator must stay untouched.
  *  - All calls on a device share the one block and it keeps whatever the last call left.  The
  *    only part that must start at zero -- a small table of arrival counters at its head -- is
  *    zero when the library loads and is left at zero by every completed call; the partial sums

@@ -19,7 +19,8 @@ b = torch.randn(N, generator=gen).to(dev, torch.bfloat16)
 A = (torch.randn(r, K, generator=gen) * 0.02).to(dev)
 B = (torch.randn(N, r, generator=gen) * 0.02).to(dev)
 dy = torch.randn(M, N, generator=gen).to(dev, torch.bfloat16)
-ws = torch.empty(bind.workspace_bytes(M, K, N, r), dtype=torch.uint8, device=dev)
+ws = torch.zeros(bind.workspace_bytes(M, K, N, r), dtype=torch.uint8, device=dev)
+packed = torch.empty(bind.packed_bytes(K, N, r), dtype=torch.uint8, device=dev)
 bkt = torch.empty(r * K + N * r, device=dev)
 dA, dB = bkt[: r * K].view(r, K), bkt[r * K:].view(N, r)
 exch = pkg.comm.PeerBucketExchange(bkt.numel()) if world > 1 else None
@@ -27,8 +28,8 @@ rng = torch.zeros(1, dtype=torch.int64, device=dev)
 
 
 def step(use_exch):
-    Y, H, keep, xd = bind.linear_fwd(x, W, b, A, B, s, p, 1, 0, False, ws, save_xd=True, offset_dev=rng)
-    bind.linear_bwd(dy, xd, W, A, B, H, keep, s, p, False, ws, need_dx=True, dA=dA, dB=dB, x_is_dropped=True)
+    Y, H, keep, _ = bind.linear_fwd(x, W, b, A, B, s, p, 1, 0, False, packed, offset_dev=rng)
+    bind.linear_bwd(dy, x, W, packed, H, keep, r, s, p, False, ws, need_dx=True, dA=dA, dB=dB)
     if use_exch and exch is not None:
         exch.allreduce_avg_(bkt)
     rng.add_(4)

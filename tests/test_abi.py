@@ -31,6 +31,9 @@ def test_host_only_entry_points(pkg):
     w2 = b.workspace_bytes(16384, 2560, 2560, 64)
     assert 0 < w1 < w2
     assert b.workspace_bytes(0, 8, 8, 8) == 0 and b.workspace_bytes(8, 8, 8, 65) == 0
+    # packed adapter operands: four 16-bit copies of [rp, K] / [N, rp], each padded to 256 bytes
+    assert b.packed_bytes(2560, 2560, 8) == 4 * 16 * 2560 * 2 and b.packed_bytes(776, 520, 33) >= 2 * 64 * (776 + 520) * 2
+    assert b.packed_bytes(0, 8, 8) == 0
     assert b.lib().lora_last_error() == b""
 
 

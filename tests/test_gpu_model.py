@@ -6,9 +6,10 @@ Per-layer outputs/gradients are held to 2e-2 in test_gpu_parity.py; here errors 
 bf16 blocks, so logits/adapter-gradients get 5e-2 on the smooth-activation GPT-2 and a direction /
 norm criterion on OPT (ReLU gates of a tiny random-init model flip between bf16 and fp32, which
 moves single gradient entries by >10 % without any kernel being wrong), and the BASELINE.json
-criterion "training loss after 50 steps within 1 %" is checked directly.  Model-level runs use lora_dropout=0 and HF
-dropouts off: CPU and GPU cannot share torch's own dropout streams (layer-level dropout parity
-with shared Philox masks is in test_gpu_parity.py)."""
+criterion "training loss after 50 steps within 1 %" is checked directly.  HF's own dropouts are off in every
+model-level run (CPU and GPU cannot share torch's dropout streams); the LoRA dropout is off in most of them and ON
+(0.05, the reference's value) in test_model_with_lora_dropout_shares_the_philox_mask, where the oracle's layers take
+their masks from oracle/philox.py at the (seed, offset) pairs the device layers draw from torch's CUDA generator."""
 import copy
 
 import numpy as np
@@ -44,12 +45,14 @@ def _opt(n_layer=2, hidden=256, ffn=1024, heads=4, vocab=512, n_pos=128):
     return OPTForCausalLM(cfg)
 
 
-def _pair(pkg, base, targets, r=8, alpha=16, dtype=torch.bfloat16):
+def _pair(pkg, base, targets, r=8, alpha=16, dtype=torch.bfloat16, dropout=0.0):
     """(oracle fp32 CPU model, fused bf16 CUDA model) with identical base weights and adapters."""
     ref = lora_ref.ref_get_peft_model(copy.deepcopy(base), lora_ref.RefLoraConfig(r=r, lora_alpha=alpha,
-                                                                               target_modules=targets))
+                                                                               target_modules=targets,
+                                                                               lora_dropout=dropout))
     ours = pkg.get_peft_model(copy.deepcopy(base).to(dtype), pkg.LoraConfig(r=r, lora_alpha=alpha,
                                                                              target_modules=targets, bias="none",
+                                                                             lora_dropout=dropout,
                                                                              task_type=pkg.TaskType.CAUSAL_LM))
     # same adapter init on both sides; B random (non-zero) so that every gradient path is exercised
     g = torch.Generator().manual_seed(7)
@@ -98,6 +101,55 @@ def test_logits_and_adapter_grads_match_oracle(pkg, arch):
             assert cos > 0.98, (n, cos)
             assert abs(float(a.norm() / b.norm()) - 1.0) < 5e-2, n
     assert all(p.grad is None for n, p in ours.named_parameters() if "lora_" not in n)  # no dW, no dbias
+
+
+def test_model_with_lora_dropout_shares_the_philox_mask(pkg):
+    """The reference's configuration (lora_dropout = 0.05, finetune_lora_distilgpt2.py:101) through a whole
+    model: the device layers take (seed, offset) from torch's CUDA generator and advance it once per call; the
+    oracle's layers are fed oracle/philox.py masks at the same (seed, offset) sequence, so both sides drop the
+    same elements and logits / loss / adapter gradients can be compared directly."""
+    import math
+
+    from oracle import philox
+
+    p, seed = 0.05, 4321
+    base = _gpt2()
+    ref, ours = _pair(pkg, base, ["c_attn", "c_proj"], dropout=p)
+    state = {"offset": 0}
+
+    def mask_fn(M, K):
+        keep = torch.from_numpy(philox.keep_mask(M, K, p, seed, state["offset"]))
+        state["offset"] += 4 * math.ceil(M * K / 32)  # lora._philox_seed_offset's advance
+        return keep
+
+    n_hooked = 0
+    for m in ref.modules():
+        if isinstance(m, lora_ref.RefLoraLinear):
+            m.mask_fn = mask_fn
+            n_hooked += 1
+    assert n_hooked == 6  # 2 blocks x (attn.c_attn, attn.c_proj, mlp.c_proj)
+    ids = torch.randint(0, 512, (4, 64), generator=torch.Generator().manual_seed(3))
+    ref.train()
+    ours.train()
+    loss_r = lora_ref.causal_lm_loss(ref(input_ids=ids).logits, ids)
+    loss_r.backward()
+    torch.cuda.manual_seed(seed)  # offset 0; nothing else on the device draws random numbers (HF dropouts are 0)
+    out_o = ours(input_ids=ids.cuda()).logits
+    loss_o = pkg.train.causal_lm_loss(out_o, ids.cuda())
+    loss_o.backward()
+    assert torch.cuda.default_generators[0].get_offset() == state["offset"]  # same number of draws on both sides
+    assert abs(float(loss_o) - float(loss_r)) / float(loss_r) < 1e-2
+    gr = {n: q.grad for n, q in ref.named_parameters() if q.requires_grad}
+    go = {n: q.grad for n, q in ours.named_parameters() if q.requires_grad}
+    assert set(gr) == set(go) and len(gr) == 12
+    worst = max(relerr(go[n], gr[n]) for n in gr)
+    assert worst < 5e-2, worst
+    # the comparison is sensitive to the mask: the oracle with ANOTHER offset sequence is visibly different
+    state["offset"] = 4
+    ref.zero_grad(set_to_none=True)
+    lora_ref.causal_lm_loss(ref(input_ids=ids).logits, ids).backward()
+    other = {n: q.grad for n, q in ref.named_parameters() if q.requires_grad}
+    assert max(relerr(go[n], other[n]) for n in gr) > 5e-2
 
 
 def test_gradient_checkpointing_replays_dropout(pkg):

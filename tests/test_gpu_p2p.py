@@ -54,6 +54,7 @@ def _worker(rank, world, port, q):
                 net.zero_grad(set_to_none=True)
                 ddp(x).square().mean().backward()
             grads[exch] = [p.grad.clone() for p in net.parameters()]
+            pkg.train.close_exchange(ddp)  # collective: own buffer and the peers' IPC mappings
             del ddp
         for a, b in zip(grads["nccl"], grads["p2p"]):
             assert torch.allclose(a, b, rtol=1e-5, atol=1e-7)

@@ -45,7 +45,7 @@ def _batches(pkg, n):
     return pkg.train.synthetic_batches(n, batch=2, seq=12, vocab=64, pad_id=1, seed=77)
 
 
-def _worker(rank, world, port, out_dir, n_layers, n_micro):
+def _worker(rank, world, port, out_dir, n_layers, n_micro, overlap):
     sys.path.insert(0, REPO_ROOT)
     os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
                       MASTER_PORT=str(port))
@@ -56,7 +56,7 @@ def _worker(rank, world, port, out_dir, n_layers, n_micro):
     pkg.train.init_distributed("gloo")
     pm = _model(n_layers)
     stage = pkg.pipeline.OPTStage(pm.base_model.model, rank, world)  # finetune_lora_opt_pp.py:116
-    eng = pkg.pipeline.PipelineEngine(stage, lr=1e-2, max_grad_norm=1.0)
+    eng = pkg.pipeline.PipelineEngine(stage, lr=1e-2, max_grad_norm=1.0, overlap=overlap)
     losses = []
     for step in range(2):
         eng.zero_grad()
@@ -72,11 +72,12 @@ def _worker(rank, world, port, out_dir, n_layers, n_micro):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,n_layers,n_micro", [(2, 4, 4), (3, 5, 2)])
-def test_pipeline_equals_unsplit_model(tmp_path, pkg, world, n_layers, n_micro):
+# overlap=True: sends and receives on per-direction communicators, nothing grouped; False: grouped blocking exchanges
+@pytest.mark.parametrize("world,n_layers,n_micro,overlap", [(2, 4, 4, True), (3, 5, 2, False)])
+def test_pipeline_equals_unsplit_model(tmp_path, pkg, world, n_layers, n_micro, overlap):
     assert pkg.pipeline.split_layers(32, 8) == [4] * 8 and pkg.pipeline.split_layers(5, 3) == [2, 2, 1]
     port = _free_port()
-    mp.spawn(_worker, args=(world, port, str(tmp_path), n_layers, n_micro), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, port, str(tmp_path), n_layers, n_micro, overlap), nprocs=world, join=True)
     ranks = [torch.load(tmp_path / f"rank{r}.pt") for r in range(world)]
     # unsplit reference: same micro-batches, accumulate, clip, AdamW -- twice
     from oracle import lora_ref

@@ -21,6 +21,20 @@ def _stale() -> bool:
     return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
 
 
+def build_variant(name: str, extra_flags) -> str:
+    """Experiment builds (scripts/ only): the same sources with extra -D flags into liblora_b200_<name>.so next to
+    the shipped library; a process selects one with LORA_B200_LIB=<path> before the first call (binding.lib)."""
+    out = os.path.join(PKG_DIR, f"liblora_b200_{name}.so")
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-shared", "-Xcompiler",
+           "-fPIC", "-I", os.path.join(REPO_ROOT, "include"), "-I", CSRC, "-o", out] + list(extra_flags) + \
+          [os.path.join(CSRC, s) for s in SOURCES]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+    return out
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     """Compile csrc/*.cu -> liblora_b200.so (sm_100a only).  Returns the library path.
     Safe when several ranks of one job call it at once: an exclusive file lock serialises the staleness check and

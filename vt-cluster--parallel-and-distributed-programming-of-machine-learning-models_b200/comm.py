@@ -1,8 +1,8 @@
 """In-stream peer-memory exchange of the adapter-gradient bucket (csrc/p2p.cuh) for one NVSwitch box.
 
 The reference leaves its one exchange step -- averaging the LoRA gradients across data-parallel
-ranks -- to torch DDP over gloo (finetune_lora_distilgpt2.py:142; launch at
-sbatch/run_finetune_distilgpt2.sbatch).  Here it is one kernel in the compute stream: every rank
+ranks -- to torch DDP over gloo (finetune_lora_distilgpt2.py:142; launched by
+"Cluster/Project 1 - Fine Tuning Distilgpt2/submit_distilgpt2_lora.sbatch").  Here it is one kernel in the compute stream: every rank
 copies its bucket into a buffer all peers have mapped (CUDA IPC), flags travel over NVLink, and each
 rank sums the peers' copies in rank order, so all replicas hold bit-identical averages.
 
@@ -74,9 +74,10 @@ class PeerBucketExchange:
         """t <- mean over ranks, in place, enqueued on the current stream (fp32, contiguous, CUDA)."""
         if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
             raise RuntimeError("allreduce_avg_ needs a contiguous fp32 CUDA tensor")
-        rc = self._lib.lora_bucket_allreduce_avg(ctypes.c_void_p(t.data_ptr()), t.numel(), self._syms, self.rank, self.world,
-                                                 self.capacity, mode,
-                                                 ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+        with binding.device_guard(t):
+            rc = self._lib.lora_bucket_allreduce_avg(ctypes.c_void_p(t.data_ptr()), t.numel(), self._syms, self.rank,
+                                                     self.world, self.capacity, mode,
+                                                     ctypes.c_void_p(binding._stream(t.device)))
         binding._check(rc, "lora_bucket_allreduce_avg")
         return t
 

@@ -31,6 +31,17 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// Explicit shared-space 16-byte accesses (pointers derived from the re-aligned dynamic smem base lose
+// their address space and would otherwise compile to generic LD/ST).
+__device__ __forceinline__ uint4 lds128(uint32_t saddr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t saddr, const uint4 v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(saddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
 // ---------------------------------------------------------------------------
 // Programmatic dependent launch: every kernel of a forward/backward call is launched with the
 // programmatic-stream-serialization attribute, signals `launch_dependents` at once (the next
@@ -232,11 +243,20 @@ __host__ __device__ __forceinline__ uint32_t make_idesc_f16(int fmt, int umma_m,
 }
 
 // ---------------------------------------------------------------------------
-// Philox4x32-10 (Salmon et al., SC'11).  One call yields 128 random bits, consumed as eight
-// 16-bit lanes of which the low 14 bits are used: one lane per element of an aligned group of
-// eight consecutive elements of the [M,K] dropout input; an element survives iff
-// lane14 >= round(p * 16384).  The same function is restated in numpy in oracle/philox.py so
-// that CPU and GPU share masks.
+// Philox4x32-10 (Salmon et al., SC'11) and the layout of the dropout stream.
+//
+// The [M,K] adapter input is cut into 16x16 element blocks (block (R,C) = rows 16R.., columns
+// 16C..).  Each block takes 32 Philox calls, one per lane of the warp that masks it; call t draws
+// for exactly the eight elements lane t holds in the A-fragment of a warp-level m16n8k16 MMA over
+// that block, so the row projection masks its fragments with its own draw and nothing is exchanged
+// between lanes:
+//     element (i, j) of the block  ->  call t = 4*(i%8) + (j%8)/2,
+//                                      16-bit lane e = 4*(j/8) + 2*(i/8) + j%2 of the 128 random bits
+// counter = (g_lo, g_hi, offset_lo, offset_hi) with g = (R * ceil(K/16) + C) * 32 + t, key = seed.
+// An element survives iff the low 14 bits of its lane are >= round(p * 16384).
+// What is STORED is layout-neutral: keep[M, K/8] bytes, bit e of byte (m, k/8) = element
+// (m, 8*(k/8) + e).  The same mapping is restated in numpy in oracle/philox.py so that CPU and GPU
+// share masks bit for bit.
 // ---------------------------------------------------------------------------
 __host__ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
                                                        uint32_t k0, uint32_t k1, uint32_t (&out)[4]) {
@@ -254,23 +274,31 @@ __host__ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1,
   }
   out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
-// keep-bits (bit e set = element e of the group survives) for group `g`; plain reference form.
-__host__ __device__ __forceinline__ uint32_t dropout_keep_bits(uint64_t g, uint64_t seed, uint64_t offset,
-                                                               uint32_t thresh14) {
-  uint32_t r[4];
-  philox4x32_10(static_cast<uint32_t>(g), static_cast<uint32_t>(g >> 32), static_cast<uint32_t>(offset),
-                static_cast<uint32_t>(offset >> 32), static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32),
-                r);
+// Philox counter of call `t` for block (row16, col16); blocks_per_row = ceil(K / 16).
+__host__ __device__ __forceinline__ uint64_t dropout_counter(uint32_t row16, uint32_t col16, uint32_t blocks_per_row,
+                                                             uint32_t t) {
+  return (static_cast<uint64_t>(row16) * blocks_per_row + col16) * 32ull + t;
+}
+// Keep-byte of row m, columns 8*c8 .. 8*c8+7; plain reference form (four calls, two bits from each).
+__host__ __device__ __forceinline__ uint32_t dropout_keep_byte(uint32_t m, uint32_t c8, uint32_t blocks_per_row,
+                                                               uint64_t seed, uint64_t offset, uint32_t thresh14) {
+  const uint32_t i = m & 15u, w = (i >> 3) + 2u * (c8 & 1u);  // 32-bit word of the draw that holds this row's pair
   uint32_t bits = 0;
 #pragma unroll
-  for (int e = 0; e < 8; ++e) {
-    const uint32_t u = (r[e >> 1] >> ((e & 1) * 16)) & 0x3FFFu;
-    bits |= (u >= thresh14 ? 1u : 0u) << e;
+  for (uint32_t q = 0; q < 4; ++q) {
+    const uint64_t g = dropout_counter(m >> 4, c8 >> 1, blocks_per_row, 4u * (i & 7u) + q);
+    uint32_t r[4];
+    philox4x32_10(static_cast<uint32_t>(g), static_cast<uint32_t>(g >> 32), static_cast<uint32_t>(offset),
+                  static_cast<uint32_t>(offset >> 32), static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32),
+                  r);
+    const uint32_t lo = r[w] & 0x3FFFu, hi = (r[w] >> 16) & 0x3FFFu;
+    bits |= (lo >= thresh14 ? 1u : 0u) << (2u * q);
+    bits |= (hi >= thresh14 ? 1u : 0u) << (2u * q + 1u);
   }
   return bits;
 }
 #ifdef __CUDACC__
-// Round keys of Philox4x32-10 for a fixed seed: hoisted out of the per-group call (the seed is a
+// Round keys of Philox4x32-10 for a fixed seed: hoisted out of the per-call rounds (the seed is a
 // kernel constant), which removes 20 adds from every draw.
 struct PhiloxKeys {
   uint32_t k[10][2];
@@ -287,17 +315,18 @@ __device__ __forceinline__ PhiloxKeys philox_round_keys(uint64_t seed) {
   }
   return rk;
 }
-// thresh14 -> the packed-half constant dropout_keep_masks compares against
+// thresh14 -> the packed-half constant dropout_fragment_masks compares against
 __host__ __device__ __forceinline__ uint32_t dropout_thresh_half2(uint32_t thresh14) {
   return (thresh14 + 0x0400u) * 0x00010001u;
 }
-// Same draw as dropout_keep_bits, delivered as four AND-masks for the four 32-bit words of a
-// 16-byte chunk of 16-bit elements (0xFFFF per surviving element) plus the packed keep-bits.
+// One draw for the calling lane: mask[w] is the AND-mask (0xFFFF per surviving 16-bit element) of
+// A-fragment register w of an m16n8k16 MMA over the block whose counter base is (g_lo, g_hi) + lane.
 // The 14-bit lanes, offset by 0x0400, are all positive NORMAL fp16 bit patterns (0x0400..0x43FF),
 // whose floating-point order equals their integer order: one HSET2 per word gives both masks.
-__device__ __forceinline__ uint32_t dropout_keep_masks(uint32_t g_lo, uint32_t g_hi, uint32_t off_lo, uint32_t off_hi,
-                                                       const PhiloxKeys& rk, uint32_t thresh_h2,
-                                                       uint32_t (&mask)[4]) {
+// Returns the eight keep-bits of the draw, bit 2w + h = element h of register w.
+__device__ __forceinline__ uint32_t dropout_fragment_masks(uint32_t g_lo, uint32_t g_hi, uint32_t off_lo,
+                                                           uint32_t off_hi, const PhiloxKeys& rk, uint32_t thresh_h2,
+                                                           uint32_t (&mask)[4]) {
   uint32_t c0 = g_lo, c1 = g_hi, c2 = off_lo, c3 = off_hi;
 #pragma unroll
   for (int i = 0; i < 10; ++i) {

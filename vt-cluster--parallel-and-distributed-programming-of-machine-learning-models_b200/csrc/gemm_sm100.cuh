@@ -44,6 +44,17 @@ struct Cfg {
   static constexpr int CTAS = kPair ? 2 : 1;
 };
 constexpr int EPI_WARPS = 4;
+// Warp roles.  The four epilogue warps must cover the four TMEM lane quadrants (warp % 4); which of the
+// two warps of a scheduler is the epilogue warp is free.  LB_EPI_FIRST = 1 gives the epilogue the LOW
+// warp ids (0..3) and the producer / MMA issuer / TMEM allocator ids 4 / 5 / 6, so that on the two
+// schedulers they share, the single-thread producer and issuer are the higher-numbered warps.
+#ifndef LB_EPI_FIRST
+#define LB_EPI_FIRST 0
+#endif
+constexpr int EPI_WARP0 = LB_EPI_FIRST ? 0 : 4;
+constexpr int PRODUCER_WARP = LB_EPI_FIRST ? 4 : 0;
+constexpr int MMA_WARP = LB_EPI_FIRST ? 5 : 1;
+constexpr int ALLOC_WARP = LB_EPI_FIRST ? 6 : 2;
 constexpr int EPI_BUF_BYTES = 32 * 128;  // 32 rows x 64 cols x 2 B
 constexpr int EPI_BYTES = EPI_WARPS * 2 * EPI_BUF_BYTES;
 constexpr int BAR_BYTES = 256;
@@ -171,7 +182,7 @@ __global__ void __launch_bounds__(THREADS, 1)
   const uint32_t cta_rank = kPair ? cluster_ctarank() : 0u;
   const bool is_leader = cta_rank == 0;
 
-  if (warp == 0 && lane == 0) {
+  if (warp == PRODUCER_WARP && lane == 0) {
     tma_prefetch_desc(&tmA1);
     tma_prefetch_desc(&tmB1);
     tma_prefetch_desc(&tmD);
@@ -180,7 +191,7 @@ __global__ void __launch_bounds__(THREADS, 1)
       tma_prefetch_desc(&tmB2);
     }
   }
-  if (warp == 1 && lane == 0) {
+  if (warp == MMA_WARP && lane == 0) {
     for (int i = 0; i < STAGES; ++i) {
       mbar_init(&full[i], C::CTAS);  // pair: leader's expect_tx arrive + the peer's remote arrive
       mbar_init(&empty[i], 1);       // one (multicast) tcgen05.commit per use
@@ -191,7 +202,7 @@ __global__ void __launch_bounds__(THREADS, 1)
     }
     fence_barrier_init();
   }
-  if (warp == 2) {
+  if (warp == ALLOC_WARP) {
     if constexpr (kPair) {
       tmem_alloc_2sm(tmem_slot, TMEM_COLS);
       tmem_relinquish_2sm();
@@ -217,7 +228,7 @@ __global__ void __launch_bounds__(THREADS, 1)
   const int tile0 = static_cast<int>(blockIdx.x) / C::CTAS;
   const int tile_step = static_cast<int>(gridDim.x) / C::CTAS;
 
-  if (warp == 0) {
+  if (warp == PRODUCER_WARP) {
     // ===================== TMA producer =====================
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
@@ -259,7 +270,7 @@ __global__ void __launch_bounds__(THREADS, 1)
       }
     }
     __syncwarp();
-  } else if (warp == 1) {
+  } else if (warp == MMA_WARP) {
     // ===================== MMA issuer =====================
     if (lane == 0 && is_leader) {
       const int fmt = (p.dtype == kDtypeBf16) ? 1 : 0;
@@ -317,9 +328,9 @@ __global__ void __launch_bounds__(THREADS, 1)
       }
     }
     __syncwarp();
-  } else if (warp >= 4) {
+  } else if (warp >= EPI_WARP0 && warp < EPI_WARP0 + EPI_WARPS) {
     // ===================== epilogue =====================
-    const int ew = warp - 4;  // == warp % 4: the TMEM lane quadrant this warp may touch
+    const int ew = warp - EPI_WARP0;  // == warp % 4: the TMEM lane quadrant this warp may touch
     uint8_t* my_stage = epi_base + ew * 2 * EPI_BUF_BYTES;
     // Masked mode, wide ranks: a 32x32 fp32 scratch per warp through which the warp-level MMA
     // result is transposed to one-row-per-thread.
@@ -761,10 +772,10 @@ __global__ void __launch_bounds__(THREADS, 1)
   tc_fence_before();
   if constexpr (kPair) {
     cluster_sync_all();  // the peer's smem / TMEM / barriers stay alive until both CTAs are done
-    if (warp == 2) tmem_dealloc_2sm(tmem_base, TMEM_COLS);
+    if (warp == ALLOC_WARP) tmem_dealloc_2sm(tmem_base, TMEM_COLS);
   } else {
     __syncthreads();
-    if (warp == 2) tmem_dealloc(tmem_base, TMEM_COLS);
+    if (warp == ALLOC_WARP) tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 

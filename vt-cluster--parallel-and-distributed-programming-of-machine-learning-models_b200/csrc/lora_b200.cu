@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <utility>
 
@@ -57,9 +58,49 @@ EncodeTiledFn encode_fn() {
   return fn;
 }
 
+// Host-side cache of encoded tensor maps (SURVEY.md 8b allows one): a training step asks for the same
+// (pointer, shape, stride, box, swizzle, dtype) descriptors again and again -- W, bias-free operands, the
+// packed adapters, activation buffers that the caching allocator hands back at the same address -- and
+// cuTensorMapEncodeTiled costs about a microsecond each, 17-19 times per layer forward+backward.
+// One small direct-mapped table per host thread (autograd's backward thread gets its own), no locks.
+// A descriptor depends on nothing but its key, so a hit can never be stale.
+struct TmapKey {
+  const void* ptr;
+  uint64_t inner, outer, stride;
+  uint32_t box_inner, box_outer;
+  int32_t dtype, swizzle;
+  bool operator==(const TmapKey& o) const {
+    return ptr == o.ptr && inner == o.inner && outer == o.outer && stride == o.stride && box_inner == o.box_inner &&
+           box_outer == o.box_outer && dtype == o.dtype && swizzle == o.swizzle;
+  }
+};
+struct TmapSlot {
+  TmapKey key{};
+  bool valid = false;
+  CUtensorMap map;
+};
+constexpr int kTmapSlots = 1024;  // power of two
+thread_local std::unique_ptr<TmapSlot[]> g_tmap_cache;
+
+inline size_t tmap_hash(const TmapKey& k) {
+  uint64_t h = reinterpret_cast<uintptr_t>(k.ptr) * 0x9E3779B97F4A7C15ull;
+  h ^= (k.inner * 0xC2B2AE3D27D4EB4Full) ^ (k.outer * 0x165667B19E3779F9ull) ^ (k.stride << 7) ^
+       (static_cast<uint64_t>(k.box_inner) << 40) ^ (static_cast<uint64_t>(k.box_outer) << 52) ^
+       (static_cast<uint64_t>(k.dtype) << 3) ^ static_cast<uint64_t>(k.swizzle);
+  h ^= h >> 29;
+  return static_cast<size_t>(h) & (kTmapSlots - 1);
+}
+
 // 2-D row-major tensor [outer, inner] of 16-bit elements, row stride in elements.
 int make_tmap(CUtensorMap* tm, const void* ptr, int dtype, uint64_t inner, uint64_t outer, uint64_t row_stride_elems,
               uint32_t box_inner, uint32_t box_outer, CUtensorMapSwizzle sw, const char* what) {
+  const TmapKey key{ptr, inner, outer, row_stride_elems, box_inner, box_outer, dtype, static_cast<int32_t>(sw)};
+  if (!g_tmap_cache) g_tmap_cache.reset(new TmapSlot[kTmapSlots]);
+  TmapSlot& slot = g_tmap_cache[tmap_hash(key)];
+  if (slot.valid && slot.key == key) {
+    *tm = slot.map;
+    return 0;
+  }
   EncodeTiledFn fn = encode_fn();
   if (!fn) return fail("cuTensorMapEncodeTiled not available from the driver");
   if ((reinterpret_cast<uintptr_t>(ptr) & 15u) != 0) return fail("%s: pointer not 16-byte aligned", what);
@@ -72,6 +113,9 @@ int make_tmap(CUtensorMap* tm, const void* ptr, int dtype, uint64_t inner, uint6
   CUresult r = fn(tm, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled(%s) failed with CUresult %d", what, (int)r);
+  slot.key = key;
+  slot.map = *tm;
+  slot.valid = true;
   return 0;
 }
 
@@ -180,17 +224,30 @@ Split colproj_split(int64_t M, int64_t launch_tiles) {
 int64_t colproj_tiles(int64_t C, int rp) { return (C + skinny::cp_cols(rp) - 1) / skinny::cp_cols(rp); }
 
 constexpr int kMaxColTiles = 4096;  // arrival counters per column projection (C <= 4096*64 columns)
-struct Workspace {
-  size_t a16, a16t, sb16, sb16t, dh, counters, partial, partial2, total;
+// Packed adapter operands (written by the forward or by lora_linear_pack, read by the backward):
+//   a16 [rp,K]   a16t [K,rp]   sb16 [N,rp] (= s*B)   sb16t [rp,N]      16-bit, rank padded to rp
+struct Packed {
+  size_t a16, a16t, sb16, sb16t, total;
 };
-Workspace carve(int64_t M, int64_t K, int64_t N, int r) {
+Packed carve_packed(int64_t K, int64_t N, int r) {
   const int rp = rpad_of(r);
-  Workspace w;
+  Packed w;
   size_t off = 0;
   w.a16 = off;   off += align256(static_cast<size_t>(rp) * K * 2);
   w.a16t = off;  off += align256(static_cast<size_t>(rp) * K * 2);
   w.sb16 = off;  off += align256(static_cast<size_t>(rp) * N * 2);
   w.sb16t = off; off += align256(static_cast<size_t>(rp) * N * 2);
+  w.total = off;
+  return w;
+}
+// Scratch of the backward: dH, the column projections' arrival counters and split partial sums.
+struct Workspace {
+  size_t dh, counters, partial, partial2, total;
+};
+Workspace carve(int64_t M, int64_t K, int64_t N, int r) {
+  const int rp = rpad_of(r);
+  Workspace w;
+  size_t off = 0;
   w.dh = off;    off += align256(static_cast<size_t>(M) * rp * 2);
   w.counters = off; off += align256(2 * kMaxColTiles * sizeof(unsigned int));
   const Split sp = colproj_split(M, colproj_tiles(K, rp) + colproj_tiles(N, rp));
@@ -210,47 +267,41 @@ int check_common(int64_t M, int64_t K, int64_t N, int r, int dtype) {
   return 0;
 }
 
-int launch_pack(const float* A, const float* B, uint8_t* ws, const Workspace& w, int64_t K, int64_t N, int r, float s,
+int launch_pack(const float* A, const float* B, uint8_t* pk, const Packed& w, int64_t K, int64_t N, int r, float s,
                 int dtype, cudaStream_t stream) {
   const int rp = rpad_of(r);
   const long long total = static_cast<long long>(rp) * (K + N);
   const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, 2048));
   if (dtype == kDtypeBf16)
     CUDA_TRY(launch_pdl(skinny::pack_adapters_kernel<__nv_bfloat16>, dim3(grid), dim3(256), 0, stream, 1, A, B,
-                        (__nv_bfloat16*)(ws + w.a16), (__nv_bfloat16*)(ws + w.a16t), (__nv_bfloat16*)(ws + w.sb16),
-                        (__nv_bfloat16*)(ws + w.sb16t), (int)K, (int)N, r, rp, s, (unsigned int*)(ws + w.counters),
-                        2 * kMaxColTiles));
+                        (__nv_bfloat16*)(pk + w.a16), (__nv_bfloat16*)(pk + w.a16t), (__nv_bfloat16*)(pk + w.sb16),
+                        (__nv_bfloat16*)(pk + w.sb16t), (int)K, (int)N, r, rp, s));
   else
     CUDA_TRY(launch_pdl(skinny::pack_adapters_kernel<__half>, dim3(grid), dim3(256), 0, stream, 1, A, B,
-                        (__half*)(ws + w.a16), (__half*)(ws + w.a16t), (__half*)(ws + w.sb16), (__half*)(ws + w.sb16t),
-                        (int)K, (int)N, r, rp, s, (unsigned int*)(ws + w.counters), 2 * kMaxColTiles));
+                        (__half*)(pk + w.a16), (__half*)(pk + w.a16t), (__half*)(pk + w.sb16), (__half*)(pk + w.sb16t),
+                        (int)K, (int)N, r, rp, s));
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
 
 template <bool BF, int RP>
-int launch_rowproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmP, const CUtensorMap& tmXd,
-                     const skinny::RowProjParams& p, cudaStream_t stream) {
+int launch_rowproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmP, const skinny::RowProjParams& p,
+                     cudaStream_t stream) {
   const int grid = (p.M + skinny::rp_rows(RP) - 1) / skinny::rp_rows(RP);
   CUDA_TRY(launch_pdl(skinny::rowproj_kernel<BF, RP>, dim3(grid), dim3(skinny::rp_threads(RP)), skinny::rp_smem_bytes<RP>(),
-                      stream, 1, tmAct, tmP, tmXd, p));
+                      stream, 1, tmAct, tmP, p));
   return 0;
 }
 
-// out[M, rp] = out_scale * (keep .* act)[M, C] * P[rp, C]^T
-int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out, void* xd_out, int64_t M, int64_t C,
-                   int rp, int dtype, float out_scale, float p, uint64_t seed, uint64_t offset, cudaStream_t stream,
-                   const uint64_t* offset_dev = nullptr) {
-  CUtensorMap tmAct, tmP, tmXd;
+// out[M, rp] = out_scale * (keep .* act)[M, C] * P[rp, C]^T; with p > 0 the keep-bits are drawn here and stored.
+// zero_words: optional block of words the kernel clears (arrival counters of the column projections).
+int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out, int64_t M, int64_t C, int rp, int dtype,
+                   float out_scale, float p, uint64_t seed, uint64_t offset, cudaStream_t stream,
+                   const uint64_t* offset_dev = nullptr, unsigned int* zero_words = nullptr, int n_zero_words = 0) {
+  CUtensorMap tmAct, tmP;
   if (make_tmap(&tmAct, act, dtype, C, M, C, skinny::RP_BK, skinny::rp_rows(rp), CU_TENSOR_MAP_SWIZZLE_128B, "rowproj act")) return 1;
   if (make_tmap(&tmP, P, dtype, C, rp, C, skinny::RP_BK, rp, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj P")) return 1;
-  if (xd_out) {
-    if (make_tmap(&tmXd, xd_out, dtype, C, M, C, skinny::RP_BK, 16, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj Xd")) return 1;
-  } else {
-    tmXd = tmAct;
-  }
   skinny::RowProjParams rp_p;
-  rp_p.store_xd = (xd_out != nullptr && p > 0.f) ? 1 : 0;
   rp_p.out = out;
   rp_p.keep_out = keep_out;
   rp_p.M = (int)M;
@@ -261,8 +312,10 @@ int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out,
   rp_p.offset = offset;
   rp_p.offset_dev = reinterpret_cast<const unsigned long long*>(offset_dev);
   rp_p.thresh14 = static_cast<uint32_t>(p * 16384.0f + 0.5f);
+  rp_p.zero_words = zero_words;
+  rp_p.n_zero_words = n_zero_words;
   const bool bf = dtype == kDtypeBf16;
-#define RP_CASE(BF, RP) return launch_rowproj_t<BF, RP>(tmAct, tmP, tmXd, rp_p, stream);
+#define RP_CASE(BF, RP) return launch_rowproj_t<BF, RP>(tmAct, tmP, rp_p, stream);
   if (bf) {
     if (rp == 16) RP_CASE(true, 16) else if (rp == 32) RP_CASE(true, 32) else RP_CASE(true, 64)
   } else {
@@ -422,13 +475,15 @@ int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, 
   const long long tiles = ((M + tile_m - 1) / tile_m) * ((N + gemm::BN - 1) / gemm::BN);
   const bool masked = p.masked_r > 0;
   if (masked && p.act) return fail("internal: activation epilogue with the masked kernel");
-  // Timing experiments only (results are wrong): LORA_B200_DEBUG_MASKED_R=j runs the masked kernel with the
-  // rank-r loop cut to j iterations, to separate the loop's cost from the rest of the masked epilogue.
+#ifdef LORA_B200_DEBUG
+  // Timing experiments only (results are wrong; never compiled into the shipped library):
+  // LORA_B200_DEBUG_MASKED_R=j runs the masked kernel with the rank-r loop cut to j iterations.
   static const int dbg_r = [] {
     const char* e = std::getenv("LORA_B200_DEBUG_MASKED_R");
     return e ? std::atoi(e) : -1;
   }();
   if (masked && dbg_r >= 0) p.masked_r = dbg_r;
+#endif
   if (pair) {
     const int grid = 2 * static_cast<int>(std::min<long long>(tiles, sm_count / 2));
     if (p.act) return launch_gemm_t<false, true, true>(tmA1, tmB1, tmA2, tmB2, tmD, tmZ, p, grid, stream);
@@ -477,10 +532,14 @@ int static_scratch_ptr(void** out) {
   return 0;
 }
 
-__global__ void keep_mask_kernel(uint8_t* keep, long long groups, uint64_t seed, uint64_t offset, uint32_t thresh14) {
-  for (long long g = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; g < groups;
-       g += static_cast<long long>(gridDim.x) * blockDim.x)
-    keep[g] = static_cast<uint8_t>(lb::dropout_keep_bits(static_cast<uint64_t>(g), seed, offset, thresh14));
+__global__ void keep_mask_kernel(uint8_t* keep, int M, int keep_ld, uint32_t blocks_per_row, uint64_t seed,
+                                 uint64_t offset, uint32_t thresh14) {
+  const long long total = static_cast<long long>(M) * keep_ld;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const uint32_t m = static_cast<uint32_t>(i / keep_ld), c8 = static_cast<uint32_t>(i % keep_ld);
+    keep[i] = static_cast<uint8_t>(lb::dropout_keep_byte(m, c8, blocks_per_row, seed, offset, thresh14));
+  }
 }
 
 }  // namespace
@@ -491,39 +550,59 @@ const char* lora_last_error(void) { return g_err.c_str(); }
 
 int32_t lora_linear_rpad(int32_t r) { return rpad_of(r); }
 
+size_t lora_linear_packed_bytes(int64_t K, int64_t N, int32_t r) {
+  if (K <= 0 || N <= 0 || r < 1 || r > 64) return 0;
+  return carve_packed(K, N, r).total;
+}
+
 size_t lora_linear_workspace_bytes(int64_t M, int64_t K, int64_t N, int32_t r) {
   if (M <= 0 || K <= 0 || N <= 0 || r < 1 || r > 64) return 0;
   return carve(M, K, N, r).total;
 }
 
+int lora_linear_pack(const float* A, const float* B, void* packed, size_t packed_bytes, int64_t K, int64_t N, int32_t r,
+                     float scaling, int32_t dtype, cudaStream_t stream) {
+  g_err.clear();
+  if (check_common(1, K, N, r, dtype)) return 1;
+  if (!A || !B || !packed) return fail("lora_linear_pack: null pointer argument");
+  const Packed w = carve_packed(K, N, r);
+  if (packed_bytes < w.total) return fail("packed-operand block too small: need %zu bytes, got %zu", w.total, packed_bytes);
+  if (reinterpret_cast<uintptr_t>(packed) & 255u) return fail("lora_linear_pack: packed must be 256-byte aligned");
+  int sms = 0;
+  if (device_setup(&sms)) return 1;
+  return launch_pack(A, B, static_cast<uint8_t*>(packed), w, K, N, r, scaling, dtype, stream);
+}
+
 int lora_linear_fwd(const void* X, const void* W, const void* bias, const float* A, const float* B, void* Y, void* H,
-                    uint8_t* keep_mask, void* Xd, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p,
-                    uint64_t seed, uint64_t offset, int32_t dtype, int32_t w_is_KN, void* workspace,
-                    size_t workspace_bytes, cudaStream_t stream) {
-  return lora_linear_fwd_devrng(X, W, bias, A, B, Y, H, keep_mask, Xd, M, K, N, r, scaling, p, seed, offset, nullptr, dtype,
-                                w_is_KN, workspace, workspace_bytes, stream);
+                    uint8_t* keep_mask, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p, uint64_t seed,
+                    uint64_t offset, int32_t dtype, int32_t w_is_KN, void* packed, size_t packed_bytes,
+                    cudaStream_t stream) {
+  return lora_linear_fwd_devrng(X, W, bias, A, B, Y, H, keep_mask, M, K, N, r, scaling, p, seed, offset, nullptr, dtype,
+                                w_is_KN, packed, packed_bytes, stream);
 }
 
 int lora_linear_fwd_devrng(const void* X, const void* W, const void* bias, const float* A, const float* B, void* Y, void* H,
-                           uint8_t* keep_mask, void* Xd, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p,
+                           uint8_t* keep_mask, int64_t M, int64_t K, int64_t N, int32_t r, float scaling, float p,
                            uint64_t seed, uint64_t offset, const uint64_t* offset_dev, int32_t dtype, int32_t w_is_KN,
-                           void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+                           void* packed, size_t packed_bytes, cudaStream_t stream) {
   g_err.clear();
   if (check_common(M, K, N, r, dtype)) return 1;
-  if (!X || !W || !A || !B || !Y || !H || !workspace) return fail("lora_linear_fwd: null pointer argument");
+  if (!X || !W || !Y || !H || !packed) return fail("lora_linear_fwd: null pointer argument");
+  if ((A == nullptr) != (B == nullptr)) return fail("lora_linear_fwd: pass both A and B, or neither (packed operands already valid)");
   if (!(p >= 0.f && p < 1.f)) return fail("dropout p must be in [0,1); got %f", (double)p);
   if (p > 0.f && !keep_mask) return fail("lora_linear_fwd: keep_mask is required when p > 0");
-  const Workspace w = carve(M, K, N, r);
-  if (workspace_bytes < w.total) return fail("workspace too small: need %zu bytes, got %zu", w.total, workspace_bytes);
+  const Packed w = carve_packed(K, N, r);
+  if (packed_bytes < w.total) return fail("packed-operand block too small: need %zu bytes, got %zu", w.total, packed_bytes);
+  if (reinterpret_cast<uintptr_t>(packed) & 255u) return fail("lora_linear_fwd: packed must be 256-byte aligned");
   int sms = 0;
   if (device_setup(&sms)) return 1;
-  uint8_t* ws = static_cast<uint8_t*>(workspace);
+  uint8_t* pk = static_cast<uint8_t*>(packed);
   const int rp = rpad_of(r);
   const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
 
-  if (phase_on(kPhasePack) && launch_pack(A, B, ws, w, K, N, r, scaling, dtype, stream)) return 1;
+  if (A != nullptr && phase_on(kPhasePack) && launch_pack(A, B, pk, w, K, N, r, scaling, dtype, stream)) return 1;
   if (phase_on(kPhaseRowProj) &&
-      launch_rowproj(X, ws + w.a16, H, keep_mask, Xd, M, K, rp, dtype, inv_keep, p, seed, offset, stream, offset_dev))
+      launch_rowproj(X, pk + w.a16, H, keep_mask, M, K, rp, dtype, inv_keep, p, seed, offset, stream, offset_dev))
     return 1;
   if (!phase_on(kPhaseGemm)) return 0;
   GemmArgs g{};
@@ -531,7 +610,7 @@ int lora_linear_fwd_devrng(const void* X, const void* W, const void* bias, const
   g.B1 = W;
   g.b_mn_major = w_is_KN ? 1 : 0;
   g.A2 = H;
-  g.B2 = ws + w.sb16;
+  g.B2 = pk + w.sb16;
   g.rp = rp;
   g.D = Y;
   g.bias = bias;
@@ -539,30 +618,34 @@ int lora_linear_fwd_devrng(const void* X, const void* W, const void* bias, const
   return launch_gemm(g, M, N, K, dtype, sms, stream);
 }
 
-int lora_linear_bwd(const void* dY, const void* X, const void* W, const float* A, const float* B, const void* H,
+int lora_linear_bwd(const void* dY, const void* X, const void* W, const void* packed, const void* H,
                     const uint8_t* keep_mask, void* dX, float* dA, float* dB, int64_t M, int64_t K, int64_t N,
                     int32_t r, float scaling, float p, int32_t dtype, int32_t w_is_KN, int32_t accumulate,
-                    int32_t x_is_dropped, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+                    void* workspace, size_t workspace_bytes, cudaStream_t stream) {
   g_err.clear();
   if (check_common(M, K, N, r, dtype)) return 1;
-  if (!dY || !X || !W || !A || !B || !H || !dA || !dB || !workspace) return fail("lora_linear_bwd: null pointer argument");
+  if (!dY || !X || !W || !packed || !H || !dA || !dB || !workspace) return fail("lora_linear_bwd: null pointer argument");
   if (!(p >= 0.f && p < 1.f)) return fail("dropout p must be in [0,1); got %f", (double)p);
   if (p > 0.f && !keep_mask) return fail("lora_linear_bwd: keep_mask is required when p > 0");
+  if (reinterpret_cast<uintptr_t>(packed) & 255u) return fail("lora_linear_bwd: packed must be 256-byte aligned");
+  const Packed pw = carve_packed(K, N, r);
   const Workspace w = carve(M, K, N, r);
   if (workspace_bytes < w.total) return fail("workspace too small: need %zu bytes, got %zu", w.total, workspace_bytes);
   int sms = 0;
   if (device_setup(&sms)) return 1;
   uint8_t* ws = static_cast<uint8_t*>(workspace);
+  const uint8_t* pk = static_cast<const uint8_t*>(packed);
   const int rp = rpad_of(r);
   const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
   const uint8_t* keep = p > 0.f ? keep_mask : nullptr;
   void* dH = ws + w.dh;
   float* partial = reinterpret_cast<float*>(ws + w.partial);
+  unsigned int* counters = reinterpret_cast<unsigned int*>(ws + w.counters);
 
-  if (phase_on(kPhasePack) && launch_pack(A, B, ws, w, K, N, r, scaling, dtype, stream)) return 1;
-  // dH[M, rp] = dY (sB)
+  // dH[M, rp] = dY (sB); the same launch clears the arrival counters of the column projections below
   if (phase_on(kPhaseRowProj) &&
-      launch_rowproj(dY, ws + w.sb16t, dH, nullptr, nullptr, M, N, rp, dtype, 1.f, 0.f, 0, 0, stream))
+      launch_rowproj(dY, pk + pw.sb16t, dH, nullptr, M, N, rp, dtype, 1.f, 0.f, 0, 0, stream, nullptr, counters,
+                     2 * kMaxColTiles))
     return 1;
   if (dX && phase_on(kPhaseGemm)) {
     GemmArgs g{};
@@ -575,24 +658,23 @@ int lora_linear_bwd(const void* dY, const void* X, const void* W, const float* A
       g.rp = 0;
       g.masked_r = r;
       g.dh = dH;
-      g.a16 = ws + w.a16t;      // [K, rp]: rank index contiguous, as the warp-MMA B-fragments want
-      g.a16_rows = ws + w.a16;  // [rp, K]: column index contiguous, for the staged fp32 slice (rp == 16)
+      g.a16 = pk + pw.a16t;      // [K, rp]: rank index contiguous, as the warp-MMA B-fragments want
+      g.a16_rows = pk + pw.a16;  // [rp, K]: column index contiguous, for the staged fp32 slice (rp == 16)
       g.keep = keep;
     } else {
       g.A2 = dH;
-      g.B2 = ws + w.a16t;
+      g.B2 = pk + pw.a16t;
       g.rp = rp;
     }
     if (launch_gemm(g, M, K, N, dtype, sms, stream)) return 1;
     // launch_gemm derives dh_ld from rp/masked_r; both give rp here.
   }
   if (!phase_on(kPhaseColProj)) return 0;
-  // dB[N, r] = s * dY^T H (H already carries 1/(1-p))  and  dA[r, K] = dH^T drop(X), one launch
-  unsigned int* counters = reinterpret_cast<unsigned int*>(ws + w.counters);
+  // dB[N, r] = s * dY^T H (H already carries 1/(1-p))  and  dA[r, K] = dH^T (keep .* X) / (1-p), one launch
   ColProjJob jobs[2];
   jobs[0] = ColProjJob{dY, H, nullptr, partial, counters, dB, N, (long long)r, 1ll, scaling};
-  jobs[1] = ColProjJob{X, dH, x_is_dropped ? nullptr : keep, reinterpret_cast<float*>(ws + w.partial2),
-                       counters + kMaxColTiles, dA, K, 1ll, (long long)K, inv_keep};
+  jobs[1] = ColProjJob{X, dH, keep, reinterpret_cast<float*>(ws + w.partial2), counters + kMaxColTiles, dA, K, 1ll,
+                       (long long)K, inv_keep};
   return launch_colproj(jobs, 2, M, r, rp, dtype, accumulate, stream);
 }
 
@@ -616,7 +698,11 @@ int lora_linear_base(const void* X, const void* W, const void* bias, void* Y, in
 int lora_linear_grad_b_static(const void* dY, const void* H, float* dB, int64_t M, int64_t N, int32_t r,
                                float scaling, int32_t dtype, int32_t accumulate, cudaStream_t stream) {
   g_err.clear();
-  if (check_common(M, /*K=*/8, N, r, dtype)) return 1;
+  if (M <= 0 || N <= 0 || M > INT32_MAX || N > INT32_MAX)
+    return fail("lora_linear_grad_b_static: M and N must be positive and below 2^31 (got %lld, %lld)", (long long)M, (long long)N);
+  if (N % 8 != 0) return fail("lora_linear_grad_b_static: N must be a multiple of 8 (16-byte rows of dY); got N=%lld", (long long)N);
+  if (r < 1 || r > 64) return fail("lora_linear_grad_b_static: rank r must be in [1, 64]; got %d", r);
+  if (dtype != kDtypeBf16 && dtype != kDtypeFp16) return fail("lora_linear_grad_b_static: dtype must be 0 (bf16) or 1 (fp16)");
   if (!dY || !H || !dB) return fail("lora_linear_grad_b_static: null pointer argument");
   const int rp = rpad_of(r);
   const Split sp = colproj_split(M, colproj_tiles(N, rp));
@@ -853,11 +939,12 @@ int lora_dropout_keep_mask(uint8_t* keep_mask, int64_t M, int64_t K, float p, ui
                            cudaStream_t stream) {
   g_err.clear();
   if (!keep_mask) return fail("lora_dropout_keep_mask: null pointer argument");
-  if (M <= 0 || K <= 0 || K % 8 != 0) return fail("lora_dropout_keep_mask: need M > 0, K > 0, K %% 8 == 0");
+  if (M <= 0 || K <= 0 || K % 8 != 0 || M > INT32_MAX || K > INT32_MAX) return fail("lora_dropout_keep_mask: need M > 0, K > 0, K %% 8 == 0");
   if (!(p >= 0.f && p < 1.f)) return fail("dropout p must be in [0,1); got %f", (double)p);
-  const long long groups = static_cast<long long>(M) * (K / 8);
-  const int grid = static_cast<int>(std::min<long long>((groups + 255) / 256, 4096));
-  keep_mask_kernel<<<grid, 256, 0, stream>>>(keep_mask, groups, seed, offset, static_cast<uint32_t>(p * 16384.0f + 0.5f));
+  const long long total = static_cast<long long>(M) * (K / 8);
+  const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, 4096));
+  keep_mask_kernel<<<grid, 256, 0, stream>>>(keep_mask, (int)M, (int)(K / 8), static_cast<uint32_t>((K + 15) / 16), seed,
+                                             offset, static_cast<uint32_t>(p * 16384.0f + 0.5f));
   CUDA_TRY(cudaGetLastError());
   return 0;
 }

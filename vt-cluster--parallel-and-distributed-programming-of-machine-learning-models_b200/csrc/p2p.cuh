@@ -34,8 +34,11 @@ namespace lb {
 namespace p2p {
 
 constexpr int MAX_WORLD = 8;
-constexpr int THREADS = 512;
-constexpr int MAX_CTAS = 64;  // all CTAs must be co-resident (they wait for each other): far below 148 SMs
+// 256-thread CTAs (60 registers each) fit beside a resident CTA of the forward GEMM (256 x 139 registers, all of
+// the SM's shared memory), so an exchange that runs on a side stream under the next step's forward does not keep
+// the GEMM's persistent CTAs off the SMs it sits on.
+constexpr int THREADS = 256;
+constexpr int MAX_CTAS = 128;  // all CTAs must become resident (they wait for each other): below 148 SMs
 constexpr int CTRL_BYTES = 1024;
 // A collective must tolerate a rank that is late for ordinary reasons (first-iteration library set-up, a slow input
 // pipeline, a garbage-collection pause): the peers' wait gives up only after 2^40 cycles (~9 minutes at 1.96 GHz),

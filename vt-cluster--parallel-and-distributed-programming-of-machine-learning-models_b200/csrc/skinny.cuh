@@ -64,9 +64,9 @@ __device__ __forceinline__ uint4 apply_keep(uint4 x, uint32_t bits) {
 
 // ---------------------------------------------------------------------------
 // pack: fp32 masters A[r,K], B[N,r] -> 16-bit operands in the four layouts the
-// kernels read (zero padded to r_pad; the scaling s is folded into B); also clears
-// the arrival counters of the column projections that follow in the same call.
+// kernels read (zero padded to r_pad; the scaling s is folded into B):
 //   a16 [r_pad,K]   a16t [K,r_pad]   sb16 [N,r_pad]   sb16t [r_pad,N]
+// Runs once per forward; the backward reads the forward's block (autograd saved-tensor semantics).
 // ---------------------------------------------------------------------------
 template <typename T>
 __device__ __forceinline__ T cvt16(float v);
@@ -82,11 +82,9 @@ __device__ __forceinline__ __half cvt16<__half>(float v) {
 template <typename T>
 __global__ void pack_adapters_kernel(const float* __restrict__ A, const float* __restrict__ B, T* __restrict__ a16,
                                      T* __restrict__ a16t, T* __restrict__ sb16, T* __restrict__ sb16t, int K, int N,
-                                     int r, int r_pad, float s, unsigned int* __restrict__ counters, int n_counters) {
+                                     int r, int r_pad, float s) {
   pdl_launch_dependents();
-  pdl_wait();  // the workspace may still be in use by the previous call's kernels
-  // the column-projection kernels of the same call count arrivals here (must start at zero)
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_counters; i += gridDim.x * blockDim.x) counters[i] = 0u;
+  pdl_wait();  // the block may still be read by kernels of an earlier call on this stream
   const long long na = static_cast<long long>(r_pad) * K;
   const long long nb = static_cast<long long>(N) * r_pad;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < na + nb;
@@ -108,18 +106,23 @@ __global__ void pack_adapters_kernel(const float* __restrict__ A, const float* _
 
 // ---------------------------------------------------------------------------
 // rowproj: Out[M, kRPad] = out_scale * (keep .* Act)[M, C] * P[kRPad, C]^T
-// One CTA per 16*SLABS rows (SLABS by padded rank, below).  The last warp is the TMA producer;
-// consumer warps w and w+SLABS form a pair that owns rows 16(w%SLABS)..+15: each masks half of the
-// slab's 16-byte chunks (one Philox call per 8 elements, drawn BEFORE waiting for the tile so the
-// ALU work hides under the TMA latency), the pair meets on a named barrier, then each takes half
-// of the tile's k16 steps.  The two partial accumulators are summed through shared memory at the end.
+// One CTA per 16*SLABS rows.  The last warp is the TMA producer; consumer warps w and w+SLABS share
+// the 16-row slab w%SLABS and split every 64-column tile between them (two k16 steps each); their two
+// partial accumulators are summed through shared memory at the end.  With dropout each lane draws ONE
+// Philox4x32-10 call per k16 step whose 128 bits are exactly the keep decisions of the eight elements
+// the lane holds in its A fragment (common.cuh, "layout of the dropout stream"): the fragment is
+// masked in registers, nothing is written back to shared memory and no barrier separates the draw
+// from the MMAs.  The draw does not depend on the data, so it is issued BEFORE the wait for the tile.
+// The keep-bits leave as bytes keep[M, C/8]: a quad (four lanes that share two rows) ORs its 2-bit
+// pieces together with two shuffles and stores one 32-bit word per row and tile.
 // ---------------------------------------------------------------------------
-// 16-row slabs per CTA.  Measured on B200 (M = 16384, C = 2560, r_pad 16): 4 slabs (64 rows, 256 CTAs)
-// 53 us with dropout / 17 us without; 1 slab (1024 small CTAs, better balance and occupancy on paper)
-// 68 / 25 us -- every CTA re-reads the P tiles from L2 and 2 KiB TMA boxes are inefficient.
+// 16-row slabs per CTA.  Measured on B200 (M = 16384, C = 2560, r_pad 16, round 1): 4 slabs (64 rows,
+// 256 CTAs) beat 1 slab (1024 small CTAs: every CTA re-reads the P tiles from L2 and 2 KiB TMA boxes
+// are inefficient) and 7 slabs (147 CTAs, one per SM: too few warps per SM).
 __host__ __device__ constexpr int rp_slabs(int rpad) { return 4; }
 __host__ __device__ constexpr int rp_rows(int rpad) { return 16 * rp_slabs(rpad); }
 __host__ __device__ constexpr int rp_threads(int rpad) { return (2 * rp_slabs(rpad) + 1) * 32; }
+__host__ __device__ constexpr int rp_min_ctas(int rpad) { return rpad <= 16 ? 3 : (rpad <= 32 ? 2 : 1); }
 constexpr int RP_BK = 64;
 constexpr int RP_STAGES = 6;
 template <int kRPad>
@@ -137,20 +140,21 @@ __host__ __device__ constexpr int rp_smem_bytes() {
 
 struct RowProjParams {
   void* out;  // [M, kRPad] 16-bit
-  uint8_t* keep_out;  // [M, C/8] or null
+  uint8_t* keep_out;  // [M, C/8] (dropout only)
   int M, C;
   float out_scale;
   int dropout;  // 0/1
-  int store_xd;  // 1: TMA-store the masked tiles (keep .* Act, unscaled) through tmXd
   uint64_t seed, offset;
   const unsigned long long* offset_dev;  // optional: *offset_dev is added to `offset` (graph-replayable RNG state)
   uint32_t thresh14;  // round(p * 16384)
+  unsigned int* zero_words;  // optional: words CTA 0 clears (the column projections' arrival counters)
+  int n_zero_words;
 };
 
 template <bool kBf16, int kRPad>
-__global__ void __launch_bounds__(rp_threads(kRPad))
+__global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
     rowproj_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constant__ CUtensorMap tmP,
-                   const __grid_constant__ CUtensorMap tmXd, const RowProjParams p) {
+                   const RowProjParams p) {
   constexpr int SLOT = rp_slot_bytes<kRPad>();
   constexpr int NB = kRPad / 8;
   constexpr int SLABS = rp_slabs(kRPad);
@@ -177,6 +181,10 @@ __global__ void __launch_bounds__(rp_threads(kRPad))
   pdl_launch_dependents();
   __syncthreads();
   pdl_wait();
+  // Arrival counters of the column projections that follow in the same call: they reset themselves,
+  // this only covers a workspace that has never been used (or a call that was cut short).
+  if (blockIdx.x == 0 && p.zero_words != nullptr)
+    for (int i = threadIdx.x; i < p.n_zero_words; i += blockDim.x) p.zero_words[i] = 0u;
 
   if (warp == RP_CONSUMERS) {
     if (lane == 0) {
@@ -198,92 +206,90 @@ __global__ void __launch_bounds__(rp_threads(kRPad))
   }
 
   const int slab = warp % SLABS;  // 16-row slab of the tile
-  const int half = warp / SLABS;  // which half of the slab's chunks / k-steps this warp takes
+  const int half = warp / SLABS;  // which two k16 steps of every tile this warp takes
+  const int g8 = lane >> 2, q = lane & 3;
   float acc[NB][4];
 #pragma unroll
   for (int n = 0; n < NB; ++n)
 #pragma unroll
     for (int e = 0; e < 4; ++e) acc[n][e] = 0.f;
 
+  // Per-lane constants of the dropout draw.
   const int keep_ld = p.C >> 3;
-  // Per-lane constants of the dropout draw: the Philox counter of chunk (m, c) is the group index
-  // g = m*(C/8) + c/8, i.e. a per-lane base plus 8 per K-block.
   PhiloxKeys rk;
-  uint64_t gbase[2] = {0, 0};
-  bool row_ok[2] = {false, false};
   const uint32_t thresh2 = dropout_thresh_half2(p.thresh14);
   const uint64_t offset = p.offset + ((p.dropout && p.offset_dev != nullptr) ? *p.offset_dev : 0ull);
   const uint32_t off_lo = static_cast<uint32_t>(offset), off_hi = static_cast<uint32_t>(offset >> 32);
+  const uint32_t blocks_per_row = static_cast<uint32_t>((p.C + 15) >> 4);
+  uint64_t gbase = 0;
   if (p.dropout) {
     rk = philox_round_keys(p.seed);
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      const int idx = half * 64 + lane + 32 * i;
-      const int m = m0 + slab * 16 + (idx >> 3);
-      row_ok[i] = m < p.M;
-      gbase[i] = static_cast<uint64_t>(m) * static_cast<uint64_t>(keep_ld) + static_cast<uint64_t>(idx & 7);
-    }
+    gbase = dropout_counter(static_cast<uint32_t>((m0 >> 4) + slab), static_cast<uint32_t>(half * 2), blocks_per_row,
+                            static_cast<uint32_t>(lane));
   }
+  // keep-bytes: lane q == 0 stores the four bytes of row g8 for this warp's half tile, q == 1 those of row g8 + 8
+  const int krow = m0 + slab * 16 + g8 + (q & 1) * 8;
+  uint8_t* kdst = p.dropout ? p.keep_out + static_cast<size_t>(krow) * keep_ld + half * 4 : nullptr;
+  const bool kstore = p.dropout && q < 2 && krow < p.M;
+  const bool kfast = ((keep_ld | static_cast<int>(reinterpret_cast<uintptr_t>(p.keep_out))) & 3) == 0;
+
+  // ldmatrix addresses inside a slot (128-byte rows, 16-byte chunks XOR-swizzled by row & 7)
+  const int a_row = slab * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+  const uint32_t a_off = static_cast<uint32_t>(a_row * 128);
+  const int a_sw = a_row & 7, a_hi = lane >> 4;
+  const int b_row = lane & 7, b_hi = (lane >> 3) & 1;
+
   uint32_t stage = 0, phase = 0;
   for (int kb = 0; kb < nk; ++kb) {
-    // keep-masks of this warp's 2 chunks per lane: independent of the data, so drawn first
-    uint32_t bits[2] = {0xFFu, 0xFFu};
     uint32_t kmask[2][4];
+    uint32_t kw[2] = {0xFFFFFFFFu, 0xFFFFFFFFu};
     if (p.dropout) {
 #pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        const int c8 = kb * (RP_BK / 8) + ((half * 64 + lane + 32 * i) & 7);  // chunk column = c/8
-        if (row_ok[i] && c8 < keep_ld) {
-          const uint64_t g = gbase[i] + static_cast<uint64_t>(kb * (RP_BK / 8));
-          bits[i] = dropout_keep_masks(static_cast<uint32_t>(g), static_cast<uint32_t>(g >> 32), off_lo, off_hi, rk,
-                                       thresh2, kmask[i]);
-          p.keep_out[g] = static_cast<uint8_t>(bits[i]);  // byte index == group index
+      for (int kk = 0; kk < 2; ++kk) {
+        const uint64_t g = gbase + static_cast<uint64_t>(kb * 4 + kk) * 32ull;
+        const uint32_t b = dropout_fragment_masks(static_cast<uint32_t>(g), static_cast<uint32_t>(g >> 32), off_lo, off_hi,
+                                                  rk, thresh2, kmask[kk]);
+        // 2-bit field of register w -> byte w of a word, at bit 2q; the quad's four pieces OR into whole bytes:
+        // byte 0 = (row g8, chunk 0), byte 1 = (row g8+8, chunk 0), byte 2 = (g8, chunk 1), byte 3 = (g8+8, chunk 1)
+        uint32_t t = (b * 0x1001u) & 0x000F000Fu;
+        t = ((t * 0x41u) & 0x03030303u) << (2 * q);
+        t |= __shfl_xor_sync(0xFFFFFFFFu, t, 1);
+        t |= __shfl_xor_sync(0xFFFFFFFFu, t, 2);
+        kw[kk] = t;
+      }
+      if (kstore) {
+        // this lane's row: chunk bytes (kk 0: c0, c1; kk 1: c0, c1) of the warp's half tile
+        const uint32_t sel = (q & 1) ? 0x7531u : 0x6420u;
+        const uint32_t word = __byte_perm(kw[0], kw[1], sel);
+        const int c8 = kb * 8 + half * 4;  // first chunk column of the word
+        uint8_t* dst = kdst + kb * 8;
+        if (kfast && c8 + 4 <= keep_ld) {
+          *reinterpret_cast<uint32_t*>(dst) = word;
+        } else {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            if (c8 + i < keep_ld) dst[i] = static_cast<uint8_t>(word >> (8 * i));
         }
       }
     }
     mbar_wait(&full[stage], phase, 12);
-    uint8_t* act = smem + stage * SLOT;
-    uint8_t* pt = act + RP_ACT_BYTES;
-    if (p.dropout) {
-#pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        const int idx = half * 64 + lane + 32 * i;
-        const int R = slab * 16 + (idx >> 3), ch = idx & 7;
-        if (bits[i] != 0xFFu) {
-          uint4* ptr = reinterpret_cast<uint4*>(act + R * 128 + ((ch ^ (R & 7)) << 4));
-          uint4 x = *ptr;
-          x.x &= kmask[i][0]; x.y &= kmask[i][1]; x.z &= kmask[i][2]; x.w &= kmask[i][3];
-          *ptr = x;
-        }
-      }
-      fence_proxy_async_smem();  // in-place writes -> visible to the TMA store / next TMA load
-      asm volatile("bar.sync %0, 64;" ::"r"(1 + slab) : "memory");  // the pair's slab is fully masked
-      if (p.store_xd && half == 0 && lane == 0) {
-        // dropout(X) (unscaled) is what backward's dA needs: save it once instead of re-masking X.
-        tma_store_2d(&tmXd, act + slab * 16 * 128, kb * RP_BK, m0 + slab * 16);
-        bulk_commit_group();
-      }
-    }
-    const uint32_t act_u = smem_u32(act), pt_u = smem_u32(pt);
+    const uint32_t act_u = smem_u32(smem + stage * SLOT), pt_u = act_u + RP_ACT_BYTES;
 #pragma unroll
     for (int kk = 0; kk < 2; ++kk) {
       const int ks = half * 2 + kk;
       uint32_t a[4];
-      {
-        const int R = slab * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
-        const int ch = ks * 2 + (lane >> 4);
-        ldsm_x4(act_u + R * 128 + ((ch ^ (R & 7)) << 4), a);
+      ldsm_x4(act_u + a_off + (((ks * 2 + a_hi) ^ a_sw) << 4), a);
+      if (p.dropout) {
+        a[0] &= kmask[kk][0]; a[1] &= kmask[kk][1]; a[2] &= kmask[kk][2]; a[3] &= kmask[kk][3];
       }
 #pragma unroll
       for (int n = 0; n < NB; ++n) {
         uint32_t b[2];
-        const int prow = n * 8 + (lane & 7);
-        const int ch = ks * 2 + ((lane >> 3) & 1);
-        ldsm_x2(pt_u + prow * 128 + ((ch ^ (prow & 7)) << 4), b);
+        const int prow = n * 8 + b_row;
+        ldsm_x2(pt_u + prow * 128 + (((ks * 2 + b_hi) ^ (prow & 7)) << 4), b);
         mma_16816<kBf16>(acc[n], a, b);
       }
     }
-    if (p.dropout && p.store_xd && half == 0 && lane == 0) bulk_wait_group_read<0>();  // slab read by its store
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[stage]);
     if (++stage == RP_STAGES) {
@@ -294,11 +300,11 @@ __global__ void __launch_bounds__(rp_threads(kRPad))
 
   // acc fragment: (row = lane/4 [+8], col = n*8 + (lane%4)*2 [+1]); half 1 hands its partial
   // sums to half 0 through smem (fixed order -> bit-reproducible).
-  const int rloc = slab * 16 + (lane >> 2);
+  const int rloc = slab * 16 + g8;
   if (half == 1) {
 #pragma unroll
     for (int n = 0; n < NB; ++n) {
-      const int col = n * 8 + (lane & 3) * 2;
+      const int col = n * 8 + q * 2;
       *reinterpret_cast<float2*>(sred + rloc * kRPad + col) = make_float2(acc[n][0], acc[n][1]);
       *reinterpret_cast<float2*>(sred + (rloc + 8) * kRPad + col) = make_float2(acc[n][2], acc[n][3]);
     }
@@ -309,7 +315,7 @@ __global__ void __launch_bounds__(rp_threads(kRPad))
     const int r0 = m0 + rloc;
 #pragma unroll
     for (int n = 0; n < NB; ++n) {
-      const int col = n * 8 + (lane & 3) * 2;
+      const int col = n * 8 + q * 2;
       const float2 o0 = *reinterpret_cast<const float2*>(sred + rloc * kRPad + col);
       const float2 o1 = *reinterpret_cast<const float2*>(sred + (rloc + 8) * kRPad + col);
       if (r0 < p.M)
@@ -328,7 +334,7 @@ __global__ void __launch_bounds__(rp_threads(kRPad))
 // grid = (ceil(C / (64*kCB)), splits).  A tile is 128 rows x kCB boxes of 64 columns (each box
 // one 128-byte-swizzled TMA load): kCB = 2 makes every row a 256-byte DRAM segment.  Warp 8 is
 // the TMA producer; consumer warp w owns rows 16w..16w+15 of every tile and all its columns;
-// partial sums of the 8 warps meet in shared memory, splits meet in reduce_partials_kernel.
+// partial sums of the 8 warps meet in shared memory; the last CTA of a column tile folds the row splits.
 // ---------------------------------------------------------------------------
 constexpr int CP_BM = 128;
 constexpr int CP_BOX_BYTES = CP_BM * 128;  // 16 KiB: 128 rows x 64 columns
@@ -461,8 +467,8 @@ __global__ void __launch_bounds__(CP_THREADS)
           const int idx = lane + 32 * i;
           const int R = warp * 16 + idx / (8 * kCB), cc = idx % (8 * kCB);  // cc: 16-byte chunk column
           if (kcur[i] != 0xFFu) {
-            uint4* ptr = reinterpret_cast<uint4*>(act + (cc >> 3) * CP_BOX_BYTES + R * 128 + (((cc & 7) ^ (R & 7)) << 4));
-            *ptr = apply_keep(*ptr, kcur[i]);
+            const uint32_t sa = smem_u32(act) + (cc >> 3) * CP_BOX_BYTES + R * 128 + (((cc & 7) ^ (R & 7)) << 4);
+            sts128(sa, apply_keep(lds128(sa), kcur[i]));
           }
         }
 #pragma unroll
@@ -560,21 +566,6 @@ __global__ void __launch_bounds__(CP_THREADS)
       float* o = p.out + static_cast<long long>(c0 + cl) * p.ld_c + static_cast<long long>(j) * p.ld_j;
       *o = p.accumulate ? (*o + p.scale * acc) : (p.scale * acc);
     }
-  }
-}
-
-// out[c*ld_c + j*ld_j] = scale * sum_split partial[split][c][j]  (+ old if accumulate), j < r
-__global__ void reduce_partials_kernel(const float* __restrict__ partial, float* __restrict__ out, int splits, int C,
-                                       int r_pad, int r, long long ld_c, long long ld_j, float scale,
-                                       int accumulate) {
-  const long long total = static_cast<long long>(C) * r;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int c = static_cast<int>(i / r), j = static_cast<int>(i % r);
-    float s = 0.f;
-    for (int sp = 0; sp < splits; ++sp) s += partial[(static_cast<size_t>(sp) * C + c) * r_pad + j];
-    float* o = out + c * ld_c + j * ld_j;
-    *o = accumulate ? (*o + scale * s) : (scale * s);
   }
 }
 

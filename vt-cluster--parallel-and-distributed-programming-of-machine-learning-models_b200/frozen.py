@@ -30,15 +30,33 @@ def _p(t):
 
 
 def _stream():
-    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return ctypes.c_void_p(binding._stream())
 
 
 def _pad8(n: int) -> int:
     return (n + 7) // 8 * 8
 
 
+def _on_device_of(argpos: int):
+    """Decorator for autograd-node bodies: run with the device of positional argument `argpos` current, so that the
+    kernels launch on that device's stream (a model on cuda:1 while cuda:0 is current must not launch on cuda:0)."""
+    import functools
+
+    def deco(fn):
+        @functools.wraps(fn)
+        def wrapped(*args, **kw):
+            t = args[argpos]
+            if not isinstance(t, torch.Tensor) or not t.is_cuda:
+                raise RuntimeError("FrozenLinear / fused loss need CUDA tensors (no CPU fallback)")
+            with binding.device_guard(t):
+                return fn(*args, **kw)
+        return wrapped
+    return deco
+
+
 class _FrozenLinearFn(torch.autograd.Function):
     @staticmethod
+    @_on_device_of(1)
     def forward(ctx, x, W, bias, w_is_KN=0):
         if not x.is_cuda:
             raise RuntimeError("FrozenLinear needs CUDA tensors (no CPU fallback)")
@@ -58,6 +76,7 @@ class _FrozenLinearFn(torch.autograd.Function):
         return ybuf.view(*x.shape[:-1], ldy)[..., :N]  # strided view when N is ragged (row stride ldy)
 
     @staticmethod
+    @_on_device_of(1)
     def backward(ctx, dy):
         (W,) = ctx.saved_tensors
         x_shape, M, K, N, w_is_KN = ctx.meta
@@ -94,6 +113,7 @@ class _FrozenActLinearFn(torch.autograd.Function):
     """y = act(x W^T + b) for a frozen W; saves the pre-activation (gelu_new) or y (relu) for dX."""
 
     @staticmethod
+    @_on_device_of(1)
     def forward(ctx, x, W, bias, act, w_is_KN):
         if not x.is_cuda:
             raise RuntimeError("FrozenLinear needs CUDA tensors (no CPU fallback)")
@@ -116,6 +136,7 @@ class _FrozenActLinearFn(torch.autograd.Function):
         return y.view(*x.shape[:-1], N)
 
     @staticmethod
+    @_on_device_of(1)
     def backward(ctx, dy):
         W, saved = ctx.saved_tensors
         x_shape, M, K, N, act, w_is_KN = ctx.meta
@@ -218,6 +239,7 @@ class _FusedCEFn(torch.autograd.Function):
     """sum_i loss_i / n_valid over rows of a [M, V] 16-bit logits matrix (row stride % 8 == 0)."""
 
     @staticmethod
+    @_on_device_of(1)
     def forward(ctx, logits2, labels1, ignore_index):
         M, V = logits2.shape
         ld = logits2.stride(0)
@@ -232,6 +254,7 @@ class _FusedCEFn(torch.autograd.Function):
         return rows.sum() / n_valid
 
     @staticmethod
+    @_on_device_of(1)
     def backward(ctx, g):
         logits2, labels1, lse, n_valid = ctx.saved_tensors
         M, V = logits2.shape

@@ -24,11 +24,13 @@ _WORKSPACES: dict = {}
 
 
 def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
-    """Per-device scratch, grown on demand.  Kernels of one stream serialise on it."""
-    key = (device.index if device.index is not None else torch.cuda.current_device())
+    """Scratch of the backward, one block per (device, stream), grown on demand: kernels of one stream serialise
+    on it, backward passes running on different streams never share one."""
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    key = (idx, binding._stream(device))
     ws = _WORKSPACES.get(key)
     if ws is None or ws.numel() < nbytes:
-        ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        ws = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
         _WORKSPACES[key] = ws
     return ws
 
@@ -55,29 +57,28 @@ class _FusedLoraLinearFn(torch.autograd.Function):
         x2 = x.reshape(-1, K)
         if not x2.is_contiguous():
             x2 = x2.contiguous()
-        M = x2.shape[0]
         N = W.shape[1] if w_is_KN else W.shape[0]
-        r = A.shape[0]
-        ws = _workspace(x.device, binding.workspace_bytes(M, K, N, r))
-        Y, H, keep, xd = binding.linear_fwd(x2, W, bias, A, B, scaling, p, seed, offset, w_is_KN, ws, save_xd=True)
-        # With dropout on, backward needs dropout(x) (for dA) and the keep-bits (for dX), not x --
-        # the same tensors torch autograd saves for peft's eager lora_A(dropout(x)).
-        ctx.save_for_backward(xd if xd is not None else x2, W, A, B, H, keep)
-        ctx.meta = (scaling, p, w_is_KN, x.shape, N)
+        with binding.device_guard(x2):
+            Y, H, keep, packed = binding.linear_fwd(x2, W, bias, A, B, scaling, p, seed, offset, w_is_KN)
+        # Saved for backward: the input itself (shared with every other projection that reads it -- q/k/v save ONE
+        # x, where stock autograd saves a dropout(x) per adapter), H, the keep-bits (1/16 of x) and the 16-bit
+        # adapter operands this forward packed (backward differentiates with the values the forward used).
+        ctx.save_for_backward(x2, W, H, keep, packed)
+        ctx.meta = (scaling, p, w_is_KN, x.shape, N, A.shape[0])
         return Y.view(*x.shape[:-1], N)
 
     @staticmethod
     def backward(ctx, dy):
-        x2, W, A, B, H, keep = ctx.saved_tensors
-        scaling, p, w_is_KN, x_shape, N = ctx.meta
+        x2, W, H, keep, packed = ctx.saved_tensors
+        scaling, p, w_is_KN, x_shape, N, r = ctx.meta
         dy2 = dy.reshape(-1, N)
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
         M, K = x2.shape
-        ws = _workspace(x2.device, binding.workspace_bytes(M, K, N, A.shape[0]))
         need_dx = ctx.needs_input_grad[0]
-        dX, dA, dB = binding.linear_bwd(dy2, x2, W, A, B, H, keep, scaling, p, w_is_KN, ws, need_dx=need_dx,
-                                        x_is_dropped=keep is not None)
+        with binding.device_guard(x2):
+            ws = _workspace(x2.device, binding.workspace_bytes(M, K, N, r))
+            dX, dA, dB = binding.linear_bwd(dy2, x2, W, packed, H, keep, r, scaling, p, w_is_KN, ws, need_dx=need_dx)
         return (dX.view(x_shape) if need_dx else None, None, None, dA, dB, None, None, None, None, None)
 
 
@@ -204,11 +205,12 @@ class Linear(nn.Module):
         if W.is_cuda and W.dtype in (torch.bfloat16, torch.float16) and W.is_contiguous():
             import ctypes
 
-            rc = binding.lib().lora_merge_weight(
-                ctypes.c_void_p(W.data_ptr()), ctypes.c_void_p(A.detach().float().contiguous().data_ptr()),
-                ctypes.c_void_p(B.detach().float().contiguous().data_ptr()), self.in_features, self.out_features,
-                A.shape[0], float(sign * self.scaling[name]), binding.dtype_code(W.dtype), int(bool(self.fan_in_fan_out)),
-                ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+            A32, B32 = A.detach().float().contiguous(), B.detach().float().contiguous()
+            with binding.device_guard(W):
+                rc = binding.lib().lora_merge_weight(
+                    ctypes.c_void_p(W.data_ptr()), ctypes.c_void_p(A32.data_ptr()), ctypes.c_void_p(B32.data_ptr()),
+                    self.in_features, self.out_features, A.shape[0], float(sign * self.scaling[name]),
+                    binding.dtype_code(W.dtype), int(bool(self.fan_in_fan_out)), ctypes.c_void_p(binding._stream(W.device)))
             binding._check(rc, "lora_merge_weight")
         else:
             W.data += sign * self.get_delta_weight(name)
@@ -226,7 +228,8 @@ class Linear(nn.Module):
 
                 return _FrozenLinearFn.apply(x.to(W.dtype), W, b, int(bool(self.fan_in_fan_out)))
             x2 = x.reshape(-1, x.shape[-1]).to(W.dtype).contiguous()
-            y = binding.linear_base(x2, W, b, self.fan_in_fan_out)
+            with binding.device_guard(x2):
+                y = binding.linear_base(x2, W, b, self.fan_in_fan_out)
             return y.view(*x.shape[:-1], self.out_features)
         name = self._active_adapter
         drop = self.lora_dropout[name]

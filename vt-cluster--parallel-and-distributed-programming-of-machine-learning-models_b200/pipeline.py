@@ -38,8 +38,12 @@ class OPTStage(nn.Module):
     """Layers [lo, hi) of an OPT decoder, plus the embeddings on the first stage and the
     final LayerNorm / lm_head / loss on the last one."""
 
-    def __init__(self, causal_lm: nn.Module, stage: int, n_stages: int, loss_fn=None):
+    def __init__(self, causal_lm: nn.Module, stage: int, n_stages: int, loss_fn=None, ignore_index: int = -100):
         super().__init__()
+        # ignore_index: label value that does not count in the loss.  -100 is what HF's collator writes over padding
+        # (finetune_lora_distilgpt2.py:114); the reference's pipeline head instead feeds token ids as labels and
+        # ignores tok.pad_token_id (finetune_lora_opt_pp.py:143-152): pass that id here to follow it.
+        self.ignore_index = int(ignore_index)
         # loss_fn(logits, labels): default torch fp32 shifted cross-entropy; on the GPU pass
         # frozen.fused_causal_lm_loss (and swap lm_head / frozen neighbours with frozen.accelerate_* first).
         self.loss_fn = loss_fn
@@ -94,16 +98,16 @@ class OPTStage(nn.Module):
             return logits
         # teacher-forcing next-token loss, finetune_lora_opt_pp.py:147-152
         if self.loss_fn is not None:
-            return self.loss_fn(logits, labels)
+            return self.loss_fn(logits, labels, ignore_index=self.ignore_index)
         return F.cross_entropy(logits[:, :-1].contiguous().float().view(-1, logits.size(-1)),
-                               labels[:, 1:].contiguous().view(-1), ignore_index=-100)
+                               labels[:, 1:].contiguous().view(-1), ignore_index=self.ignore_index)
 
 
 class PipelineEngine:
     """`train_batch(micro_batches)` = one optimiser step over m micro-batches, 1F1B."""
 
     def __init__(self, stage_module: OPTStage, group=None, lr: float = 5e-5, max_grad_norm: float = 1.0,
-                 act_dtype: Optional[torch.dtype] = None, device: Optional[torch.device] = None):
+                 act_dtype: Optional[torch.dtype] = None, device: Optional[torch.device] = None, overlap: bool = True):
         self.m = stage_module
         self.group = group
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -119,10 +123,42 @@ class PipelineEngine:
         self.act_dtype = act_dtype or p0.dtype
         self.prev = self.rank - 1 if self.rank > 0 else None
         self.next = self.rank + 1 if self.rank < self.world - 1 else None
+        # overlap: activations and gradients travel on two communicators of their own (one per direction), each
+        # send is enqueued without waiting and only a receive makes the compute stream wait for data.  With one
+        # communicator the two directions between a pair of neighbours share an ordered queue, which is why the
+        # serial mode (overlap=False) must group "send forward + receive backward" into one blocking exchange.
+        self.overlap = bool(overlap) and self.world > 1
+        self.g_fwd = self.g_bwd = None
+        if self.overlap:
+            ranks = dist.get_process_group_ranks(group) if group is not None else list(range(self.world))
+            self.g_fwd = dist.new_group(ranks=ranks)  # collective: every stage constructs its engine
+            self.g_bwd = dist.new_group(ranks=ranks)
+        self._inflight = []  # (work, tensor) of sends that have not been waited for
+        self.p2p_bytes = 0   # bytes this stage sent + received in the last train_batch (for the bench)
 
     # ---- point-to-point -----------------------------------------------------------------
+    def _send(self, t, peer, g):
+        t = t.contiguous()
+        self._inflight.append((dist.isend(t, peer, group=g), t))
+        self.p2p_bytes += t.numel() * t.element_size()
+
+    def _recv(self, shape, peer, g):
+        buf = torch.empty(shape, dtype=self.act_dtype, device=self.device)
+        dist.irecv(buf, peer, group=g).wait()  # NCCL: the compute stream waits, the host does not
+        self.p2p_bytes += buf.numel() * buf.element_size()
+        return buf
+
     def _p2p(self, send_fwd=None, send_bwd=None, recv_fwd_shape=None, recv_bwd_shape=None):
-        """One grouped exchange with both neighbours (ncclGroupStart/End under NCCL)."""
+        """The exchanges with both neighbours that are due at one point of the schedule."""
+        if self.overlap:
+            if send_bwd is not None:
+                self._send(send_bwd, self.prev, self.g_bwd)
+            if send_fwd is not None:
+                self._send(send_fwd, self.next, self.g_fwd)
+            out_f = self._recv(recv_fwd_shape, self.prev, self.g_fwd) if recv_fwd_shape is not None else None
+            out_b = self._recv(recv_bwd_shape, self.next, self.g_bwd) if recv_bwd_shape is not None else None
+            return out_f, out_b
+        # serial mode: one grouped exchange (ncclGroupStart/End under NCCL), waited for as a whole
         ops, out_f, out_b = [], None, None
         if send_bwd is not None:
             ops.append(dist.P2POp(dist.isend, send_bwd.contiguous(), self.prev, self.group))
@@ -135,6 +171,8 @@ class PipelineEngine:
             out_b = torch.empty(recv_bwd_shape, dtype=self.act_dtype, device=self.device)
             ops.append(dist.P2POp(dist.irecv, out_b, self.next, self.group))
         if ops:
+            for op in ops:
+                self.p2p_bytes += op.tensor.numel() * op.tensor.element_size()
             for w in dist.batch_isend_irecv(ops):
                 w.wait()
         return out_f, out_b
@@ -150,6 +188,7 @@ class PipelineEngine:
         neighbour will only match after its own send completes."""
         m = len(micro_batches)
         S, s = self.world, self.rank
+        self.p2p_bytes = 0
         mb, seq = micro_batches[0]["input_ids"].shape
         hshape = (mb, seq, self.m.hidden_size)
         warm = min(S - 1 - s, m)
@@ -208,6 +247,9 @@ class PipelineEngine:
             gx = bwd(g)
             self._p2p(send_bwd=gx)
 
+        for w, _ in self._inflight:  # every send has left (NCCL: stream-level wait) before its buffer can be reused
+            w.wait()
+        self._inflight.clear()
         # global gradient-norm clip across stages (each adapter lives on exactly one stage)
         sq = torch.zeros((), dtype=torch.float32, device=self.device)
         for p in self.params:

@@ -89,6 +89,16 @@ def wrap_ddp(model: nn.Module, device: Optional[torch.device] = None, bucket_cap
     return DDP(model, **kw)
 
 
+def close_exchange(ddp: nn.Module) -> None:
+    """Collective: release the peer-memory exchange a `wrap_ddp(..., exchange="p2p")` wrapper holds (its own
+    buffer and the IPC mappings of every peer's).  Call it on every rank before dropping the wrapper; a wrapper
+    that used NCCL has nothing to release."""
+    ex = getattr(ddp, "_lora_exchange", None)
+    if ex is not None:
+        ex.close()
+        ddp._lora_exchange = None
+
+
 class Trainer:
     """Minimal stand-in for transformers.Trainer on this path (model(**batch) -> loss, backward,
     accumulate, reduce, clip, AdamW, linear decay)."""
@@ -135,6 +145,10 @@ class Trainer:
     def train(self, batches: Iterable[Dict]) -> List[torch.Tensor]:
         batches = list(batches)
         accum = self.cfg.accum
+        if len(batches) % accum != 0:
+            # HF Trainer would still step on a short last accumulation group; this loop divides every loss by
+            # `accum`, so a silent partial group would be mis-scaled.  Refuse instead of dropping batches.
+            raise ValueError(f"{len(batches)} micro-batches is not a multiple of accum={accum}")
         n_steps = len(batches) // accum
         self._ensure_sched(n_steps)
         self.model.train()
@@ -161,6 +175,7 @@ def save_run(model: nn.Module, save_dir: str, meta: Optional[Dict] = None, token
     on = dist.is_available() and dist.is_initialized()
     if on:
         dist.barrier()
+    close_exchange(model)
     if not on or dist.get_rank() == 0:
         core = model.module if hasattr(model, "module") and hasattr(model.module, "save_pretrained") else model
         core.save_pretrained(save_dir)
