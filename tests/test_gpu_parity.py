@@ -5,9 +5,11 @@ max relative error in bf16/fp16 against the fp32 CPU oracle fed the same 16-bit-
 and the SAME dropout mask (oracle/philox.py restates the device generator).  Two numbers are
 checked against that bound, both 2e-2:
   * relerr     = max|gpu - ref| / max|ref|                      (error relative to the tensor's scale)
-  * relerr_el  = max_i |gpu_i - ref_i| / max(|ref_i|, FLOOR * max|ref|)   (per-element relative error;
-                 elements smaller than FLOOR = 1e-2 of the largest are measured against that floor,
-                 since a 16-bit result cannot hold a relative bound on values that cancel to ~0)
+  * relerr_vec = the same ratio taken separately for every vector along the tensor's long dimension -- every
+                 token row of Y / H / dX, every rank row of dA [r,K], every rank column of dB [N,r] -- worst
+                 vector reported: no row may hide behind a larger one.  (A bound relative to each single
+                 ELEMENT is not meaningful for sums that pass through 16-bit H / dH: elements that cancel
+                 to ~0 carry the absolute rounding error of their row.)
 Integer/bit work (the keep-bits) must match exactly.
 """
 import os
@@ -21,7 +23,6 @@ from oracle import lora_ref, philox
 pytestmark = pytest.mark.gpu
 
 TOL = 2e-2
-FLOOR = 1e-2
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "lora_linear_golden.npz")
 
 
@@ -31,11 +32,16 @@ def relerr(a, ref):
     return float((a - ref).abs().max() / ref.abs().max().clamp_min(1e-20))
 
 
-def relerr_el(a, ref):
+def relerr_vec(a, ref):
     a = a.detach().float().cpu()
     ref = ref.detach().float().cpu()
-    scale = ref.abs().max().clamp_min(1e-20)
-    return float(((a - ref).abs() / ref.abs().clamp_min(FLOOR * scale)).max())
+    dim = 1 if ref.shape[1] >= ref.shape[0] or ref.shape[1] > 64 else 0  # reduce over the long dimension
+    num = (a - ref).abs().amax(dim=dim)
+    den = ref.abs().amax(dim=dim)
+    ok = den > 0
+    if not bool(ok.any()):
+        return float(num.max())
+    return float((num[ok] / den[ok]).max()) if bool((num[~ok] == 0).all()) else float("inf")
 
 
 def make_case(M, K, N, r, w_is_KN, dtype, bias=True, seed=0, b_zero=False):
@@ -137,7 +143,7 @@ def _all_errs(out, ref, r):
     pairs = {"y": (out["Y"], ref["y"]), "h": (out["H"][:, :r], ref["h"]), "dx": (out["dX"], ref["dx"]),
              "dA": (out["dA"], ref["dA"]), "dB": (out["dB"], ref["dB"])}
     errs = {k: relerr(a, b) for k, (a, b) in pairs.items()}
-    errs.update({k + "_el": relerr_el(a, b) for k, (a, b) in pairs.items()})
+    errs.update({k + "_vec": relerr_vec(a, b) for k, (a, b) in pairs.items()})
     return errs
 
 
@@ -161,7 +167,7 @@ def test_golden_fixture_through_the_gpu(pkg):
         case = dict(x=t("x"), W=t("W"), b=t("b"), A=t("A"), B=t("B"), dy=t("dy"))
         out, _ = _run_fwd_bwd(pkg, M, K, N, r, p, bool(kn), torch.bfloat16, True, seed=seed, offset=offset, case=case)
         for name, got in (("y", out["Y"]), ("dx", out["dX"]), ("dA", out["dA"]), ("dB", out["dB"])):
-            assert relerr(got, t(name)) < TOL and relerr_el(got, t(name)) < TOL, (i, name)
+            assert relerr(got, t(name)) < TOL and relerr_vec(got, t(name)) < TOL, (i, name)
 
 
 def test_step0_known_answers(pkg):
@@ -251,7 +257,7 @@ def test_full_size_against_fp32_matmul(pkg, M, K, N, w_is_KN):
     dh = s * (dyf @ d["B"])
     dx_ref = dyf @ Wnk + (dh @ d["A"]) * bits / (1 - p)
     for got, want in ((Y, y_ref), (dX, dx_ref), (dA, dh.t() @ xd), (dB, s * (dyf.t() @ h))):
-        assert relerr(got, want) < TOL and relerr_el(got, want) < TOL
+        assert relerr(got, want) < TOL and relerr_vec(got, want) < TOL
     # the keep-bits at full size: spot rows against the numpy generator (the whole mask is 42 M elements)
     rows = [0, 1, 17, M // 2 + 3, M - 1]
     assert np.array_equal(bits[rows].cpu().numpy().astype(bool), philox.keep_rows(rows, K, p, 5, 8))

@@ -31,15 +31,23 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
-// Explicit shared-space 16-byte accesses (pointers derived from the re-aligned dynamic smem base lose
-// their address space and would otherwise compile to generic LD/ST).
-__device__ __forceinline__ uint4 lds128(uint32_t saddr) {
-  uint4 v;
-  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr));
+// Explicit shared-space 8-byte accesses and the 8-byte asynchronous global -> shared copy (cp.async, LDGSTS)
+// used for the small keep-byte side stream of the column projection.
+__device__ __forceinline__ uint2 lds64(uint32_t saddr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(saddr));
   return v;
 }
-__device__ __forceinline__ void sts128(uint32_t saddr, const uint4 v) {
-  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(saddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+__device__ __forceinline__ void sts64(uint32_t saddr, const uint2 v) {
+  asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(saddr), "r"(v.x), "r"(v.y) : "memory");
+}
+__device__ __forceinline__ void cp_async8(uint32_t saddr, const void* gptr) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(saddr), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
 // ---------------------------------------------------------------------------
@@ -328,14 +336,26 @@ __device__ __forceinline__ uint32_t dropout_fragment_masks(uint32_t g_lo, uint32
                                                            uint32_t off_hi, const PhiloxKeys& rk, uint32_t thresh_h2,
                                                            uint32_t (&mask)[4]) {
   uint32_t c0 = g_lo, c1 = g_hi, c2 = off_lo, c3 = off_hi;
+#ifndef LB_EXP_PHILOX_ROUNDS
+#define LB_EXP_PHILOX_ROUNDS 10  // experiment builds only (timing); the shipped library always runs 10 rounds
+#endif
 #pragma unroll
-  for (int i = 0; i < 10; ++i) {
+  for (int i = 0; i < LB_EXP_PHILOX_ROUNDS; ++i) {
+#ifdef LB_EXP_PHILOX_MULHI
+    const uint32_t p0l = 0xD2511F53u * c0, p0h = __umulhi(0xD2511F53u, c0);
+    const uint32_t p1l = 0xCD9E8D57u * c2, p1h = __umulhi(0xCD9E8D57u, c2);
+    const uint32_t n0 = p1h ^ c1 ^ rk.k[i][0];
+    const uint32_t n2 = p0h ^ c3 ^ rk.k[i][1];
+    c1 = p1l;
+    c3 = p0l;
+#else
     const uint64_t p0 = static_cast<uint64_t>(0xD2511F53u) * c0;
     const uint64_t p1 = static_cast<uint64_t>(0xCD9E8D57u) * c2;
     const uint32_t n0 = static_cast<uint32_t>(p1 >> 32) ^ c1 ^ rk.k[i][0];
     const uint32_t n2 = static_cast<uint32_t>(p0 >> 32) ^ c3 ^ rk.k[i][1];
     c1 = static_cast<uint32_t>(p1);
     c3 = static_cast<uint32_t>(p0);
+#endif
     c0 = n0;
     c2 = n2;
   }

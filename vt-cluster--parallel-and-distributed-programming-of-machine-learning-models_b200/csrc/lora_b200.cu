@@ -212,7 +212,10 @@ struct Split {
 Split colproj_split(int64_t M, int64_t launch_tiles) {
   const int64_t m_tiles = (M + skinny::CP_BM - 1) / skinny::CP_BM;
   // two CTAs fit per SM: aim for at most one full wave (2*148 CTAs) so that no straggler wave forms
-  int64_t want = (2 * 148) / launch_tiles;
+#ifndef LB_EXP_CP_SLOTS
+#define LB_EXP_CP_SLOTS (2 * 148)
+#endif
+  int64_t want = LB_EXP_CP_SLOTS / launch_tiles;
   if (want < 1) want = 1;
   if (want > m_tiles) want = m_tiles;
   const int64_t tiles_per = (m_tiles + want - 1) / want;

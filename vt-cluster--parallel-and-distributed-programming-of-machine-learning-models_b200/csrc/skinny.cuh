@@ -51,17 +51,6 @@ __device__ __forceinline__ void mma_16816(float (&d)[4], const uint32_t (&a)[4],
         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
   }
 }
-// Zero the 16-bit lanes of a 16-byte chunk whose keep-bit is clear.
-__device__ __forceinline__ uint4 apply_keep(uint4 x, uint32_t bits) {
-  uint32_t w[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-  for (int e = 0; e < 4; ++e) {
-    const uint32_t lo = (bits >> (2 * e)) & 1u, hi = (bits >> (2 * e + 1)) & 1u;
-    w[e] &= (lo ? 0x0000FFFFu : 0u) | (hi ? 0xFFFF0000u : 0u);
-  }
-  return make_uint4(w[0], w[1], w[2], w[3]);
-}
-
 // ---------------------------------------------------------------------------
 // pack: fp32 masters A[r,K], B[N,r] -> 16-bit operands in the four layouts the
 // kernels read (zero padded to r_pad; the scaling s is folded into B):
@@ -122,9 +111,15 @@ __global__ void pack_adapters_kernel(const float* __restrict__ A, const float* _
 __host__ __device__ constexpr int rp_slabs(int rpad) { return 4; }
 __host__ __device__ constexpr int rp_rows(int rpad) { return 16 * rp_slabs(rpad); }
 __host__ __device__ constexpr int rp_threads(int rpad) { return (2 * rp_slabs(rpad) + 1) * 32; }
-__host__ __device__ constexpr int rp_min_ctas(int rpad) { return rpad <= 16 ? 3 : (rpad <= 32 ? 2 : 1); }
+#ifndef LB_EXP_RP_MIN_CTAS
+#define LB_EXP_RP_MIN_CTAS 2  // measured: capping registers for a third CTA (72, spills) 64 us, uncapped 39 us
+#endif
+#ifndef LB_EXP_RP_STAGES
+#define LB_EXP_RP_STAGES 6
+#endif
+__host__ __device__ constexpr int rp_min_ctas(int rpad) { return rpad <= 16 ? LB_EXP_RP_MIN_CTAS : (rpad <= 32 ? 2 : 1); }
 constexpr int RP_BK = 64;
-constexpr int RP_STAGES = 6;
+constexpr int RP_STAGES = LB_EXP_RP_STAGES;
 template <int kRPad>
 __host__ __device__ constexpr int rp_act_bytes() {
   return ((rp_rows(kRPad) * 128 + 1023) / 1024) * 1024;
@@ -240,61 +235,74 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
   const int b_row = lane & 7, b_hi = (lane >> 3) & 1;
 
   uint32_t stage = 0, phase = 0;
-  for (int kb = 0; kb < nk; ++kb) {
-    uint32_t kmask[2][4];
-    uint32_t kw[2] = {0xFFFFFFFFu, 0xFFFFFFFFu};
+  // Two tiles per trip: their four Philox draws are independent dependency chains (10 rounds of a wide multiply
+  // feeding a 3-input XOR each), issued back to back so that they hide one another's latency; with ~4 warps per
+  // scheduler a single chain per warp leaves the issue slots idle (ncu: "wait" and "math pipe throttle" stalls).
+  for (int kb0 = 0; kb0 < nk; kb0 += 2) {
+    uint32_t kmask[2][2][4];
     if (p.dropout) {
+      uint32_t kw[2][2];
 #pragma unroll
-      for (int kk = 0; kk < 2; ++kk) {
-        const uint64_t g = gbase + static_cast<uint64_t>(kb * 4 + kk) * 32ull;
-        const uint32_t b = dropout_fragment_masks(static_cast<uint32_t>(g), static_cast<uint32_t>(g >> 32), off_lo, off_hi,
-                                                  rk, thresh2, kmask[kk]);
-        // 2-bit field of register w -> byte w of a word, at bit 2q; the quad's four pieces OR into whole bytes:
-        // byte 0 = (row g8, chunk 0), byte 1 = (row g8+8, chunk 0), byte 2 = (g8, chunk 1), byte 3 = (g8+8, chunk 1)
-        uint32_t t = (b * 0x1001u) & 0x000F000Fu;
-        t = ((t * 0x41u) & 0x03030303u) << (2 * q);
-        t |= __shfl_xor_sync(0xFFFFFFFFu, t, 1);
-        t |= __shfl_xor_sync(0xFFFFFFFFu, t, 2);
-        kw[kk] = t;
-      }
+      for (int u = 0; u < 2; ++u)
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk) {
+          const uint64_t g = gbase + static_cast<uint64_t>((kb0 + u) * 4 + kk) * 32ull;
+          const uint32_t b = dropout_fragment_masks(static_cast<uint32_t>(g), static_cast<uint32_t>(g >> 32), off_lo,
+                                                    off_hi, rk, thresh2, kmask[u][kk]);
+          // 2-bit field of register w -> byte w of a word, at bit 2q; the quad's four pieces OR into whole bytes:
+          // byte 0 = (row g8, chunk 0), byte 1 = (row g8+8, chunk 0), byte 2 = (g8, chunk 1), byte 3 = (g8+8, chunk 1)
+          uint32_t t = (b * 0x1001u) & 0x000F000Fu;
+          t = ((t * 0x41u) & 0x03030303u) << (2 * q);
+          t |= __shfl_xor_sync(0xFFFFFFFFu, t, 1);
+          t |= __shfl_xor_sync(0xFFFFFFFFu, t, 2);
+          kw[u][kk] = t;
+        }
       if (kstore) {
         // this lane's row: chunk bytes (kk 0: c0, c1; kk 1: c0, c1) of the warp's half tile
         const uint32_t sel = (q & 1) ? 0x7531u : 0x6420u;
-        const uint32_t word = __byte_perm(kw[0], kw[1], sel);
-        const int c8 = kb * 8 + half * 4;  // first chunk column of the word
-        uint8_t* dst = kdst + kb * 8;
-        if (kfast && c8 + 4 <= keep_ld) {
-          *reinterpret_cast<uint32_t*>(dst) = word;
-        } else {
 #pragma unroll
-          for (int i = 0; i < 4; ++i)
-            if (c8 + i < keep_ld) dst[i] = static_cast<uint8_t>(word >> (8 * i));
+        for (int u = 0; u < 2; ++u) {
+          const int kb = kb0 + u;
+          const uint32_t word = __byte_perm(kw[u][0], kw[u][1], sel);
+          const int c8 = kb * 8 + half * 4;  // first chunk column of the word
+          uint8_t* dst = kdst + kb * 8;
+          if (kfast && c8 + 4 <= keep_ld) {
+            *reinterpret_cast<uint32_t*>(dst) = word;
+          } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              if (c8 + i < keep_ld) dst[i] = static_cast<uint8_t>(word >> (8 * i));
+          }
         }
       }
     }
-    mbar_wait(&full[stage], phase, 12);
-    const uint32_t act_u = smem_u32(smem + stage * SLOT), pt_u = act_u + RP_ACT_BYTES;
 #pragma unroll
-    for (int kk = 0; kk < 2; ++kk) {
-      const int ks = half * 2 + kk;
-      uint32_t a[4];
-      ldsm_x4(act_u + a_off + (((ks * 2 + a_hi) ^ a_sw) << 4), a);
-      if (p.dropout) {
-        a[0] &= kmask[kk][0]; a[1] &= kmask[kk][1]; a[2] &= kmask[kk][2]; a[3] &= kmask[kk][3];
-      }
+    for (int u = 0; u < 2; ++u) {
+      if (kb0 + u >= nk) break;
+      mbar_wait(&full[stage], phase, 12);
+      const uint32_t act_u = smem_u32(smem + stage * SLOT), pt_u = act_u + RP_ACT_BYTES;
 #pragma unroll
-      for (int n = 0; n < NB; ++n) {
-        uint32_t b[2];
-        const int prow = n * 8 + b_row;
-        ldsm_x2(pt_u + prow * 128 + (((ks * 2 + b_hi) ^ (prow & 7)) << 4), b);
-        mma_16816<kBf16>(acc[n], a, b);
+      for (int kk = 0; kk < 2; ++kk) {
+        const int ks = half * 2 + kk;
+        uint32_t a[4];
+        ldsm_x4(act_u + a_off + (((ks * 2 + a_hi) ^ a_sw) << 4), a);
+        if (p.dropout) {
+          a[0] &= kmask[u][kk][0]; a[1] &= kmask[u][kk][1]; a[2] &= kmask[u][kk][2]; a[3] &= kmask[u][kk][3];
+        }
+#pragma unroll
+        for (int n = 0; n < NB; ++n) {
+          uint32_t b[2];
+          const int prow = n * 8 + b_row;
+          ldsm_x2(pt_u + prow * 128 + (((ks * 2 + b_hi) ^ (prow & 7)) << 4), b);
+          mma_16816<kBf16>(acc[n], a, b);
+        }
       }
-    }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[stage]);
-    if (++stage == RP_STAGES) {
-      stage = 0;
-      phase ^= 1;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[stage]);
+      if (++stage == RP_STAGES) {
+        stage = 0;
+        phase ^= 1;
+      }
     }
   }
 
@@ -343,15 +351,21 @@ constexpr int CP_THREADS = (CP_CONSUMERS + 1) * 32;
 // 64-column boxes per tile / ring depth, by padded rank (register and smem budget)
 __host__ __device__ constexpr int cp_boxes(int rpad) { return 1; }  // 2 boxes cost the second resident CTA (smem)
 __host__ __device__ constexpr int cp_cols(int rpad) { return 64 * cp_boxes(rpad); }
-__host__ __device__ constexpr int cp_stages(int rpad) { return 4; }
+#ifndef LB_EXP_CP_STAGES
+#define LB_EXP_CP_STAGES 4
+#endif
+__host__ __device__ constexpr int cp_stages(int rpad) { return LB_EXP_CP_STAGES; }
 template <int kRPad>
 __host__ __device__ constexpr int cp_slot_bytes() {
   return cp_boxes(kRPad) * CP_BOX_BYTES + ((CP_BM * kRPad * 2 + 1023) / 1024) * 1024;
 }
+constexpr int CP_KEEP_STAGES = 4;  // keep-byte ring of the dA problem: 4 tiles x 128 rows x 8 bytes
+constexpr int CP_KEEP_BYTES = CP_KEEP_STAGES * CP_BM * 8;
 template <int kRPad>
 __host__ __device__ constexpr int cp_smem_bytes() {
-  return cp_stages(kRPad) * cp_slot_bytes<kRPad>() + cp_cols(kRPad) * kRPad * 4 + 1024 + 256;
+  return cp_stages(kRPad) * cp_slot_bytes<kRPad>() + cp_cols(kRPad) * kRPad * 4 + CP_KEEP_BYTES + 1024 + 256;
 }
+__host__ __device__ constexpr int cp_min_ctas(int rpad) { return rpad <= 16 ? 2 : 1; }
 
 struct ColProjProblem {
   float* partial;          // [splits][C][kRPad] split partial sums (scratch)
@@ -372,7 +386,7 @@ struct ColProjParams {
 };
 
 template <bool kBf16, int kRPad>
-__global__ void __launch_bounds__(CP_THREADS)
+__global__ void __launch_bounds__(CP_THREADS, cp_min_ctas(kRPad))
     colproj_kernel(const __grid_constant__ CUtensorMap tmAct0, const __grid_constant__ CUtensorMap tmSmall0,
                    const __grid_constant__ CUtensorMap tmAct1, const __grid_constant__ CUtensorMap tmSmall1,
                    const ColProjParams pp) {
@@ -391,7 +405,8 @@ __global__ void __launch_bounds__(CP_THREADS)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   float* sout = reinterpret_cast<float*>(smem + STAGES * SLOT);
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * SLOT + COLS * kRPad * 4);
+  uint8_t* keep_s = smem + STAGES * SLOT + COLS * kRPad * 4;  // [CP_KEEP_STAGES][128 rows][8 bytes]
+  uint64_t* full = reinterpret_cast<uint64_t*>(keep_s + CP_KEEP_BYTES);
   uint64_t* empty = full + STAGES;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -440,41 +455,61 @@ __global__ void __launch_bounds__(CP_THREADS)
         for (int e = 0; e < 4; ++e) acc[cbk][n][e] = 0.f;
 
     const int keep_ld = p.C >> 3;
-    // keep-bytes of this warp's 16 rows x (8*kCB) chunks (4*kCB per lane), fetched one tile ahead so
-    // the global-load latency never sits between a tile's arrival and its MMAs.
-    constexpr int NK = 4 * kCB;
-    auto load_keep = [&](int mt, uint32_t (&kb)[NK]) {
+    // Dropout mask of the activation (dA = dH^T drop(X)): applied to the transposed ldmatrix fragments in
+    // registers.  Register a[j] of a 16x16 block holds the two elements (rows 2q, 2q+1 [+8], one column g) of
+    // one 16-byte chunk; their keep-bits are bit g of that chunk's keep-byte in rows 2q and 2q+1.  A warp
+    // needs the 8 keep-bytes (64 columns) of each of its 16 rows per tile: lanes 0..15 copy them, 8 bytes
+    // each, into a small ring in shared memory with cp.async three tiles ahead (the loads come from HBM -- the
+    // step streams far more than L2 between the forward that wrote them and this kernel -- and no register is
+    // held while they are in flight); the ring slice of a warp is private to it, so a warp-level sync suffices.
+    static_assert(kCB == 1, "the register masking below assumes 64-column tiles");
+    constexpr int PF = CP_KEEP_STAGES - 1;
+    const int g8 = lane >> 2, q4 = lane & 3;
+    const bool has_keep = p.keep != nullptr;
+    const bool kfast = has_keep && (((keep_ld | static_cast<int>(reinterpret_cast<uintptr_t>(p.keep))) & 7) == 0) &&
+                       c0 + 64 <= p.C;
+    const uint32_t keep_u = smem_u32(keep_s) + warp * 16 * 8;
+    auto issue_keep = [&](int t) {  // keep-bytes of tile t -> ring slot t % CP_KEEP_STAGES (lanes 0..15: one row each)
+      if (t < nt && lane < 16) {
+        const int m = m_begin + t * CP_BM + warp * 16 + lane;
+        const uint32_t dst = keep_u + (t % CP_KEEP_STAGES) * (CP_BM * 8) + lane * 8;
+        const uint8_t* src = p.keep + static_cast<size_t>(m) * keep_ld + (c0 >> 3);
+        if (m < p.M && kfast) {
+          cp_async8(dst, src);
+        } else {
+          uint32_t w[2] = {0xFFFFFFFFu, 0xFFFFFFFFu};
+          if (m < p.M) {
 #pragma unroll
-      for (int i = 0; i < NK; ++i) {
-        const int idx = lane + 32 * i;  // chunk id within the warp's slab: row = idx / (8*kCB)
-        const int m = mt + warp * 16 + idx / (8 * kCB), c = c0 + (idx % (8 * kCB)) * 8;
-        kb[i] = (m < p.M && c < p.C) ? __ldg(p.keep + static_cast<size_t>(m) * keep_ld + (c >> 3)) : 0xFFu;
+            for (int c = 0; c < 8; ++c)
+              if ((c0 >> 3) + c < keep_ld)
+                w[c >> 2] = (w[c >> 2] & ~(0xFFu << (8 * (c & 3)))) | (static_cast<uint32_t>(__ldg(src + c)) << (8 * (c & 3)));
+          }
+          sts64(dst, make_uint2(w[0], w[1]));
+        }
       }
+      cp_async_commit();  // one group per tile, also when this lane copied nothing: the counting stays uniform
     };
-    uint32_t kcur[NK], knext[NK];
-#pragma unroll
-    for (int i = 0; i < NK; ++i) kcur[i] = knext[i] = 0xFFu;
-    if (p.keep != nullptr && nt > 0) load_keep(m_begin, kcur);
+    if (has_keep)
+      for (int t = 0; t < PF; ++t) issue_keep(t);
     uint32_t stage = 0, phase = 0;
     for (int t = 0; t < nt; ++t) {
       const int mt = m_begin + t * CP_BM;
-      if (p.keep != nullptr && t + 1 < nt) load_keep(mt + CP_BM, knext);
+      // per row and 32-bit half: byte c = 0xFF iff bit g8 of chunk c's keep-byte is set
+      uint32_t ksel[4][2];
+      if (has_keep) {
+        issue_keep(t + PF);
+        cp_async_wait<PF>();  // this lane's copy for tile t has landed
+        __syncwarp();         // ... and so have the other lanes' (the slice is this warp's own)
+        const uint32_t src = keep_u + (t % CP_KEEP_STAGES) * (CP_BM * 8);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint2 kr = lds64(src + ((j >> 1) * 8 + 2 * q4 + (j & 1)) * 8);
+          ksel[j][0] = ((kr.x >> g8) & 0x01010101u) * 0xFFu;
+          ksel[j][1] = ((kr.y >> g8) & 0x01010101u) * 0xFFu;
+        }
+      }
       mbar_wait(&full[stage], phase, 22);
       uint8_t* act = smem + stage * SLOT;
-      if (p.keep != nullptr) {
-#pragma unroll
-        for (int i = 0; i < NK; ++i) {
-          const int idx = lane + 32 * i;
-          const int R = warp * 16 + idx / (8 * kCB), cc = idx % (8 * kCB);  // cc: 16-byte chunk column
-          if (kcur[i] != 0xFFu) {
-            const uint32_t sa = smem_u32(act) + (cc >> 3) * CP_BOX_BYTES + R * 128 + (((cc & 7) ^ (R & 7)) << 4);
-            sts128(sa, apply_keep(lds128(sa), kcur[i]));
-          }
-        }
-#pragma unroll
-        for (int i = 0; i < NK; ++i) kcur[i] = knext[i];
-        __syncwarp();
-      }
       // Rows of the last tile of a split that belong to the next split (or lie
       // beyond M, where TMA filled zeros) must not contribute.
       const int valid_rows = m_end - mt;  // > 0
@@ -508,12 +543,20 @@ __global__ void __launch_bounds__(CP_THREADS)
           const int mrow = warp * 16 + (q >> 1) * 8 + i;
           const int ch = (cbk & 3) * 2 + (q & 1);
           ldsm_x4_t(act_u + (cbk >> 2) * CP_BOX_BYTES + mrow * 128 + ((ch ^ (mrow & 7)) << 4), a);
+          if (has_keep) {
+            // a[0]: rows (2q, 2q+1), chunk 2*cbk; a[1]: same rows, chunk 2*cbk + 1; a[2], a[3]: rows + 8
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int chunk = 2 * cbk + (j & 1), rows = (j >> 1) * 2, c = chunk & 3;
+              const uint32_t sel = static_cast<uint32_t>(((4 + c) << 12) | ((4 + c) << 8) | (c << 4) | c);
+              a[j] &= __byte_perm(ksel[rows][chunk >> 2], ksel[rows + 1][chunk >> 2], sel);
+            }
+          }
 #pragma unroll
           for (int n = 0; n < NB; ++n) mma_16816<kBf16>(acc[cbk][n], a, b[n]);
         }
       }
-      if (p.keep != nullptr) fence_proxy_async_smem();
-      __syncwarp();
+      __syncwarp();  // also: every lane has read its keep rows before the ring slot is refilled (next trip's issue)
       if (lane == 0) mbar_arrive(&empty[stage]);
       if (++stage == STAGES) {
         stage = 0;
