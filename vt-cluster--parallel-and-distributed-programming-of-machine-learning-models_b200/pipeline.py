@@ -137,14 +137,18 @@ class PipelineEngine:
         self.p2p_bytes = 0   # bytes this stage sent + received in the last train_batch (for the bench)
 
     # ---- point-to-point -----------------------------------------------------------------
+    # Each transfer is a one-element batch: under NCCL a batched P2P op runs on the pair's own communicator,
+    # whereas an unbatched isend/irecv on an eagerly initialised group is queued behind every other op of the group.
     def _send(self, t, peer, g):
         t = t.contiguous()
-        self._inflight.append((dist.isend(t, peer, group=g), t))
+        for w in dist.batch_isend_irecv([dist.P2POp(dist.isend, t, peer, g)]):
+            self._inflight.append((w, t))
         self.p2p_bytes += t.numel() * t.element_size()
 
     def _recv(self, shape, peer, g):
         buf = torch.empty(shape, dtype=self.act_dtype, device=self.device)
-        dist.irecv(buf, peer, group=g).wait()  # NCCL: the compute stream waits, the host does not
+        for w in dist.batch_isend_irecv([dist.P2POp(dist.irecv, buf, peer, g)]):
+            w.wait()  # NCCL: the compute stream waits, the host does not
         self.p2p_bytes += buf.numel() * buf.element_size()
         return buf
 
