@@ -131,6 +131,76 @@ def test_opt_layer_with_frozen_neighbours_matches_stock_path(pkg):
         assert float(torch.nn.functional.cosine_similarity(a, b, dim=0)) > 0.98, n  # bf16 + relu: see test_gpu_model
 
 
+@pytest.mark.parametrize("B,S,K,V,chunk,dtype", [(2, 33, 64, 1003, 16, torch.bfloat16),  # ragged vocab, ragged last chunk
+                                                 (4, 128, 768, 50257, 256, torch.bfloat16),  # distilgpt2 head
+                                                 (3, 17, 128, 512, 0, torch.float16)])  # default chunk (one chunk)
+def test_chunked_head_loss_matches_oracle(pkg, B, S, K, V, chunk, dtype):
+    """lm_head + shifted cross-entropy in token chunks (no [M, V] logits): loss and d(loss)/d(hidden) against the
+    fp32 CPU formula F.linear -> lora_ref.causal_lm_loss on the same 16-bit-rounded operands
+    (finetune_lora_distilgpt2.py:114, finetune_lora_opt_pp.py:143-153)."""
+    g = torch.Generator().manual_seed(4)
+    hidden = torch.randn(B, S, K, generator=g).to(dtype)
+    W = (torch.randn(V, K, generator=g) * 0.05).to(dtype)
+    labels = torch.randint(0, V, (B, S), generator=g)
+    labels[0, 3:6] = -100
+    h_ref = hidden.float().requires_grad_(True)
+    ref = lora_ref.causal_lm_loss(torch.nn.functional.linear(h_ref, W.float()), labels)
+    (ref * 0.5).backward()
+    h = hidden.cuda().requires_grad_(True)
+    loss = pkg.frozen.chunked_head_loss(h, W.cuda(), labels.cuda(), chunk_tokens=chunk)
+    (loss * 0.5).backward()
+    assert abs(float(loss) - float(ref)) / abs(float(ref)) < 2e-3
+    assert h.grad.shape == (B, S, K)
+    assert relerr(h.grad, h_ref.grad) < TOL
+    assert float(h.grad[:, -1].float().abs().max()) == 0.0  # the last position has no target
+    # and against the two-kernel path that does materialise the logits
+    h2 = hidden.cuda().requires_grad_(True)
+    lin = torch.nn.Linear(K, V, bias=False).to(dtype).cuda()
+    with torch.no_grad():
+        lin.weight.copy_(W.cuda())
+    lin.weight.requires_grad_(False)
+    loss2 = pkg.frozen.fused_causal_lm_loss(pkg.frozen.FrozenLinear(lin)(h2), labels.cuda())
+    (loss2 * 0.5).backward()
+    assert abs(float(loss) - float(loss2)) < 1e-5 * abs(float(loss2)) + 1e-6
+    assert relerr(h.grad, h2.grad) < 1e-2
+
+
+def test_model_with_deferred_head_matches_materialised_path(pkg):
+    """fuse_lm_head_with_loss on a GPT-2-style model: same loss and adapter gradients as lm_head + fused CE."""
+    from transformers import GPT2Config, GPT2LMHeadModel
+
+    torch.manual_seed(0)
+    base = GPT2LMHeadModel(GPT2Config(n_layer=2, n_embd=256, n_head=4, vocab_size=1003, n_positions=64,
+                                      resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0)).to(torch.bfloat16)
+    cfg = pkg.LoraConfig(r=8, lora_alpha=16, target_modules=["c_attn", "c_proj"], task_type=pkg.TaskType.CAUSAL_LM)
+    ids = torch.randint(0, 1003, (2, 48), generator=torch.Generator().manual_seed(2)).cuda()
+    res = []
+    for deferred in (False, True):
+        torch.manual_seed(5)
+        pm = pkg.get_peft_model(copy.deepcopy(base), cfg).cuda()
+        with torch.no_grad():
+            for n, p in pm.named_parameters():
+                if "lora_B" in n:
+                    p.copy_(torch.randn(p.shape, generator=torch.Generator().manual_seed(3)).to(p.device) * 0.02)
+        if deferred:
+            loss_fn = pkg.frozen.fuse_lm_head_with_loss(pm, chunk_tokens=32)
+            assert isinstance(pm.base_model.model.lm_head, pkg.frozen.DeferredHead)
+        else:
+            pkg.frozen.accelerate_lm_head(pm)
+            loss_fn = pkg.frozen.fused_causal_lm_loss
+        pm.train()
+        loss = loss_fn(pm(input_ids=ids).logits, ids)
+        loss.backward()
+        res.append((float(loss), {n: p.grad.clone() for n, p in pm.named_parameters() if p.requires_grad}))
+        if deferred:  # eval mode: the deferred head is the plain frozen projection again
+            pm.eval()
+            with torch.no_grad():
+                assert pm(input_ids=ids).logits.shape == (2, 48, 1003)
+    assert abs(res[0][0] - res[1][0]) / res[0][0] < 1e-3
+    for n in res[0][1]:
+        assert relerr(res[1][1][n], res[0][1][n]) < 2e-2, n
+
+
 def test_model_with_fast_head_and_loss_matches_stock_path(pkg):
     """distilgpt2-style model with a ragged vocab: swapping lm_head + loss changes nothing but speed."""
     from transformers import GPT2Config, GPT2LMHeadModel

@@ -282,3 +282,123 @@ def fused_causal_lm_loss(logits: torch.Tensor, labels: torch.Tensor, ignore_inde
         buf[:, :V].copy_(logits.reshape(B * S, V))
         l2 = buf[:, :V]
     return _FusedCEFn.apply(l2, shifted.reshape(-1), int(ignore_index))
+
+
+# ----------------------------------------------------------------------------------------------
+# lm_head fused with the loss in token chunks (SURVEY.md 8f row N2 as written): the [M, V] logits never exist.
+# ----------------------------------------------------------------------------------------------
+class _ChunkedHeadCEFn(torch.autograd.Function):
+    """loss = mean_{labels != ignore} CE(hidden W^T (+ b), shifted labels), computed chunk by chunk: for every
+    block of `chunk` tokens the head GEMM writes its logits into ONE reused buffer (sized to stay in L2), the
+    cross-entropy forward reads them, its backward overwrites them in place with dlogits / n_valid, and the
+    head's dX GEMM consumes those -- four launches per chunk on the kernels above, no [M, V] tensor in HBM
+    (distilgpt2 at 16 x 1024 tokens: 1.65 GB of logits and as much again of dlogits).  The weight is frozen, so the
+    only gradient is dX; it is complete when forward returns, backward just scales it."""
+
+    @staticmethod
+    @_on_device_of(1)
+    def forward(ctx, hidden, W, bias, labels1, ignore_index, chunk):
+        K = hidden.shape[-1]
+        V = W.shape[0]
+        h2 = hidden.reshape(-1, K)
+        if not h2.is_contiguous():
+            h2 = h2.contiguous()
+        M = h2.shape[0]
+        dev, code = h2.device, binding.dtype_code(h2.dtype)
+        ldv = _pad8(V)
+        need_dx = ctx.needs_input_grad[0]
+        lse = torch.empty(M, dtype=torch.float32, device=dev)
+        rows = torch.empty(M, dtype=torch.float32, device=dev)
+        n_valid = (labels1 != ignore_index).sum().clamp_min(1).to(torch.float32)
+        scale = (1.0 / n_valid).reshape(1).contiguous()
+        dX = torch.empty((M, K), dtype=h2.dtype, device=dev) if need_dx else None
+        buf = torch.empty((min(chunk, M), ldv), dtype=h2.dtype, device=dev)
+        lib, st, esz = binding.lib(), _stream(), h2.element_size()
+        for c0 in range(0, M, chunk):
+            m = min(chunk, M - c0)
+            hp = ctypes.c_void_p(h2.data_ptr() + c0 * K * esz)
+            lp = ctypes.c_void_p(labels1.data_ptr() + c0 * 8)
+            lsep = ctypes.c_void_p(lse.data_ptr() + c0 * 4)
+            rc = lib.lora_frozen_linear_fwd(hp, K, _p(W), _p(bias), _p(buf), ldv, m, K, V, code, 0, st)
+            binding._check(rc, "lora_frozen_linear_fwd")
+            rc = lib.lora_ce_fwd(_p(buf), ldv, lp, lsep, ctypes.c_void_p(rows.data_ptr() + c0 * 4), m, V, ignore_index, code, st)
+            binding._check(rc, "lora_ce_fwd")
+            if need_dx:
+                rc = lib.lora_ce_bwd(_p(buf), ldv, lp, lsep, _p(scale), _p(buf), ldv, m, V, ignore_index, code, st)
+                binding._check(rc, "lora_ce_bwd")
+                rc = lib.lora_frozen_linear_bwd(_p(buf), ldv, _p(W), ctypes.c_void_p(dX.data_ptr() + c0 * K * esz), K, m, K, V,
+                                                code, 0, st)
+                binding._check(rc, "lora_frozen_linear_bwd")
+        ctx.save_for_backward(dX)
+        ctx.hshape = hidden.shape
+        return rows.sum() / n_valid
+
+    @staticmethod
+    def backward(ctx, g):
+        (dX,) = ctx.saved_tensors
+        if dX is None:
+            return None, None, None, None, None, None
+        return (dX * g.to(dX.dtype)).view(ctx.hshape), None, None, None, None, None
+
+
+def chunked_head_loss(hidden: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor, bias=None,
+                      ignore_index: int = -100, chunk_tokens: int = 0) -> torch.Tensor:
+    """hidden [B, S, K] (16-bit, CUDA), weight [V, K] frozen, labels [B, S] -> scalar fp32 causal-LM loss
+    (next-token, labels shifted here) without materialising the logits.  chunk_tokens = 0: as many tokens per
+    chunk as keep the logits buffer within 96 MiB (it lives in the 126 MB L2 between the four kernels)."""
+    if not hidden.is_cuda or hidden.dtype not in (torch.bfloat16, torch.float16):
+        raise RuntimeError("chunked_head_loss needs 16-bit CUDA hidden states (no CPU fallback)")
+    if weight.requires_grad:
+        raise RuntimeError("chunked_head_loss is for a frozen head: it produces no weight gradient")
+    B, S, _ = hidden.shape
+    V = weight.shape[0]
+    if chunk_tokens <= 0:
+        chunk_tokens = max(256, ((96 << 20) // (_pad8(V) * hidden.element_size())) // 256 * 256)
+    shifted = torch.full((B, S), ignore_index, dtype=torch.long, device=hidden.device)
+    shifted[:, :-1] = labels[:, 1:]
+    return _ChunkedHeadCEFn.apply(hidden, weight, bias, shifted.reshape(-1), int(ignore_index), int(chunk_tokens))
+
+
+class DeferredHead(nn.Module):
+    """Stands in for `lm_head` while training with `chunked_head_loss`: forward hands the hidden states through
+    unchanged (the model's "logits" output then carries hidden states, which the paired loss function turns into the
+    loss); in eval mode it is the plain frozen projection.  Shares the base layer's Parameters (weight tying survives)."""
+
+    def __init__(self, base: nn.Linear):
+        super().__init__()
+        if base.weight.requires_grad:
+            raise ValueError("DeferredHead is for a frozen lm_head")
+        self.base_layer = base
+        self._plain = FrozenLinear(base)
+
+    @property
+    def weight(self):
+        return self.base_layer.weight
+
+    @property
+    def bias(self):
+        return self.base_layer.bias
+
+    def forward(self, hidden):
+        return hidden if self.training else self._plain(hidden)
+
+
+def fuse_lm_head_with_loss(model: nn.Module, chunk_tokens: int = 0):
+    """Swap `lm_head` for a DeferredHead and return the loss function to pair with it:
+    `loss_fn(model(**batch).logits, labels)` -- same call shape as fused_causal_lm_loss -- computes the chunked
+    head + cross-entropy.  Training mode only (eval returns real logits)."""
+    for holder in (model, getattr(model, "base_model", None), getattr(getattr(model, "base_model", None), "model", None)):
+        if holder is None:
+            continue
+        head = holder.__dict__.get("_modules", {}).get("lm_head")
+        if isinstance(head, FrozenLinear):
+            head = head.base_layer
+        if isinstance(head, nn.Linear):
+            dh = DeferredHead(head)
+            holder.lm_head = dh
+
+            def loss_fn(hidden, labels, ignore_index: int = -100):
+                return chunked_head_loss(hidden, dh.weight, labels, dh.bias, ignore_index, chunk_tokens)
+
+            return loss_fn
+    raise ValueError("no nn.Linear lm_head found")
