@@ -63,6 +63,12 @@ def parse():
                          "NCCL all-reduce (layer workload: on a side stream overlapped with the next step; models: torch DDP)")
     ap.add_argument("--no-graph", action="store_true",
                     help="layer workload: launch every step eagerly instead of replaying one captured CUDA graph per step")
+    ap.add_argument("--head", choices=["chunked", "materialised"], default="chunked",
+                    help="model workloads: lm_head + loss in token chunks without [M, V] logits (default), or lm_head "
+                         "through the tcgen05 GEMM followed by the fused cross-entropy over materialised logits")
+    ap.add_argument("--head-chunk", type=int, default=0, help="tokens per chunk of the chunked head (0: fit 96 MiB)")
+    ap.add_argument("--no-plain-neighbours", action="store_true",
+                    help="model workloads: leave un-adapted frozen projections without an activation on cuBLAS")
     ap.add_argument("--stock-head", action="store_true",
                     help="model workloads: keep torch's lm_head matmul and fp32 cross-entropy (default: lm_head through "
                          "the tcgen05 GEMM + fused cross-entropy, SURVEY 8f rows N2/N3)")
@@ -616,7 +622,8 @@ def model_workload_name(a, B, S, world):
     return (f"{a.workload} architecture (random init) LoRA r=8 alpha=16 dropout=0.05 fine-tune step, "
             f"gradient checkpointing {'off' if a.no_ckpt else 'on'}, batch {B} x seq {S} per GPU, "
             f"{('DDP, adapter bucket averaged by ' + ('the in-stream peer-memory kernel, ' if a.exchange == 'p2p' else 'NCCL all-reduce, ')) if world > 1 else ''}AdamW lr 5e-5 + clip 1.0, "
-            f"{'stock torch lm_head + fp32 CE' if a.stock_head else 'lm_head on the tcgen05 GEMM + fused CE'}")
+            f"{'stock torch lm_head + fp32 CE' if a.stock_head else ('chunked lm_head + CE (no [M,V] logits)' if a.head == 'chunked' else 'lm_head on the tcgen05 GEMM + fused CE over materialised logits')}"
+            f"{'' if a.stock_head or a.no_plain_neighbours else ', every frozen projection of the blocks on the tcgen05 GEMM'}")
 
 
 def run_model(a, pkg, rank, world, device, with_e2e=True):
@@ -637,9 +644,15 @@ def run_model(a, pkg, rank, world, device, with_e2e=True):
     n_lora = len(pm.base_model.lora_layers())
     loss_fn = None
     if not a.stock_head:
-        pkg.frozen.accelerate_lm_head(pm)
-        pkg.frozen.accelerate_frozen_neighbours(pm)
-        loss_fn = pkg.frozen.fused_causal_lm_loss
+        # lm_head fused with the loss in token chunks (no [M, V] logits), frozen neighbours of the
+        # adapters (c_fc + gelu_new, fc1 + relu, and for OPT q/v the un-targeted k_proj / out_proj / fc2) on this
+        # library's tcgen05 GEMM instead of cuBLAS
+        if a.head == "chunked":
+            loss_fn = pkg.frozen.fuse_lm_head_with_loss(pm, chunk_tokens=a.head_chunk)
+        else:
+            pkg.frozen.accelerate_lm_head(pm)
+            loss_fn = pkg.frozen.fused_causal_lm_loss
+        pkg.frozen.accelerate_frozen_neighbours(pm, plain=not a.no_plain_neighbours)
     net = pkg.train.wrap_ddp(pm, device, exchange=a.exchange) if world > 1 else pm
     tr = pkg.train.Trainer(net, pkg.train.TrainConfig(lr=5e-5, accum=1, total_steps=10 ** 6), loss_fn=loss_fn)
     tr._ensure_sched(10 ** 6)
@@ -738,8 +751,11 @@ def run_pipeline(a, pkg, rank, world, device):
                                                  target_modules=targets, task_type=pkg.TaskType.CAUSAL_LM))
     loss_fn = None
     if not a.stock_head:
-        pkg.frozen.accelerate_lm_head(pm)
-        loss_fn = pkg.frozen.fused_causal_lm_loss
+        if a.head == "chunked":
+            loss_fn = pkg.frozen.fuse_lm_head_with_loss(pm, chunk_tokens=a.head_chunk)
+        else:
+            pkg.frozen.accelerate_lm_head(pm)
+            loss_fn = pkg.frozen.fused_causal_lm_loss
     stage = pkg.pipeline.OPTStage(pm.base_model.model, rank, world, loss_fn=loss_fn)
     stage.to_empty(device=device)
     gen = torch.Generator(device=device).manual_seed(1 + rank)
@@ -826,7 +842,7 @@ def run_pipeline(a, pkg, rank, world, device):
         "config": {"workload": f"OPT-2.7B architecture (random init) LoRA r=8 alpha=16 dropout=0.05 on six targets, "
                                f"pipeline-parallel: {layers} layers over {world} stages, 1F1B, {best['m']} micro-batches of "
                                f"{mb} x {seq} tokens per optimiser step, AdamW + clip 1.0, "
-                               f"{'stock torch lm_head + fp32 CE' if a.stock_head else 'lm_head on the tcgen05 GEMM + fused CE'}",
+                               f"{'stock torch lm_head + fp32 CE' if a.stock_head else ('chunked lm_head + CE' if a.head == 'chunked' else 'lm_head on the tcgen05 GEMM + fused CE')}",
                    "split": pkg.pipeline.split_layers(layers, world), "parallelism": f"pp{world}", "global_batch": best["m"] * mb,
                    "seq_len": seq, "l2_policy": "activations + weights far larger than L2"},
         "clocks": clk_summary,

@@ -200,6 +200,24 @@ int lora_act_bwd(const void* dY, const void* ZorY, void* dZ, int64_t n_elems, in
                  cudaStream_t stream);
 
 /*
+ * Optimiser step of the adapter parameters in two launches: global gradient-norm clip + AdamW over every adapter
+ * tensor.  Replaces torch.nn.utils.clip_grad_norm_ + torch.optim.AdamW.step as HF Trainer / DeepSpeed run them for
+ * the reference (finetune_lora_distilgpt2.py:130-145: lr 5e-5, betas (0.9, 0.999), eps 1e-8, weight_decay 0,
+ * max_grad_norm 1.0; finetune_lora_opt_pp.py:193-197), same formulas: coef = min(1, max_norm / (norm + 1e-6)),
+ * g *= coef (stored back), p *= 1 - lr wd, m = b1 m + (1-b1) g, v = b2 v + (1-b2) g^2,
+ * p -= lr / (1 - b1^step) * m / (sqrt(v) / sqrt(1 - b2^step) + eps).
+ * `table` is a DEVICE array of n_tensors rows of six 64-bit words {param ptr, grad ptr, exp_avg ptr, exp_avg_sq ptr,
+ * element count, first chunk} (all tensors fp32, contiguous; first chunk = sum over earlier rows of
+ * ceil(count / LORA_ADAMW_CHUNK)); n_chunks is that sum over all rows.  `scratch`: 4 + n_chunks floats, zeroed once
+ * by the caller; after the call scratch[0] holds the gradient norm before clipping, scratch[1] the clip factor.
+ * step counts from 1.  max_grad_norm <= 0 disables clipping.
+ */
+#define LORA_ADAMW_CHUNK 4096
+int lora_adamw_clip_step(const void* table, int32_t n_tensors, int64_t n_chunks, float lr, float beta1, float beta2,
+                         float eps, float weight_decay, int32_t step, float max_grad_norm, float* scratch,
+                         cudaStream_t stream);
+
+/*
  * The path's one exchange step under DDP: average the flat fp32 adapter-gradient bucket (dA|dB of every
  * adapted layer) over the GPUs of one NVLink/NVSwitch box, in the caller's stream, through peer memory.
  * Replaces the gloo/NCCL all-reduce torch DDP issues for the reference
