@@ -36,6 +36,7 @@ class TrainConfig:
     eps: float = 1e-8
     weight_decay: float = 0.0
     constant_lr: bool = False  # the OPT pipeline script keeps lr constant (finetune_lora_opt_pp.py:207)
+    fused_optimizer: bool = True  # CUDA: clip + AdamW as two launches of this library; False: torch.optim.AdamW
 
 
 def causal_lm_loss(logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
@@ -99,6 +100,74 @@ def close_exchange(ddp: nn.Module) -> None:
         ddp._lora_exchange = None
 
 
+class FusedAdamW:
+    """Gradient-norm clip + AdamW of every adapter tensor in two kernel launches (C ABI lora_adamw_clip_step,
+    csrc/optim.cuh) instead of the ~30 small kernels of clip_grad_norm_ + torch.optim.AdamW: on distilgpt2 the
+    optimiser step is otherwise launch-bound.  Same formulas and defaults as the torch pair (HF Trainer's, which the
+    reference uses: finetune_lora_distilgpt2.py:130-145).  CUDA fp32 parameters only; no CPU path."""
+
+    def __init__(self, params, lr=5e-5, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, max_grad_norm=1.0):
+        from . import binding
+
+        self.params = [p for p in params]
+        if not self.params or any((not p.is_cuda) or p.dtype != torch.float32 or not p.is_contiguous() for p in self.params):
+            raise RuntimeError("FusedAdamW needs contiguous fp32 CUDA parameters (no CPU fallback)")
+        self.lr, self.betas, self.eps, self.weight_decay, self.max_grad_norm = lr, betas, eps, weight_decay, max_grad_norm
+        self.device = self.params[0].device
+        self.exp_avg = [torch.zeros_like(p) for p in self.params]
+        self.exp_avg_sq = [torch.zeros_like(p) for p in self.params]
+        self.steps = 0
+        self._binding = binding
+        self._key, self._table, self._n_chunks, self._scratch = None, None, 0, None
+
+    def _build_table(self, live):
+        chunk = 4096  # LORA_ADAMW_CHUNK
+        rows, first = [], 0
+        for i in live:
+            p = self.params[i]
+            rows.append([p.data_ptr(), p.grad.data_ptr(), self.exp_avg[i].data_ptr(), self.exp_avg_sq[i].data_ptr(),
+                         p.numel(), first])
+            first += (p.numel() + chunk - 1) // chunk
+        self._table = torch.tensor(rows, dtype=torch.int64).to(self.device)
+        if self._scratch is None or self._scratch.numel() < 4 + first:
+            self._scratch = torch.zeros(4 + first, dtype=torch.float32, device=self.device)
+        self._n_chunks = first
+
+    def step(self, lr=None):
+        """One optimiser step over the parameters that have a gradient; returns the pre-clip gradient norm (a CUDA
+        scalar view, no host sync)."""
+        import ctypes
+
+        live = [i for i, p in enumerate(self.params) if p.grad is not None]
+        if not live:
+            return None
+        for i in live:
+            g = self.params[i].grad
+            if g.dtype != torch.float32 or not g.is_contiguous():
+                self.params[i].grad = g = g.float().contiguous()
+        key = tuple((i, self.params[i].data_ptr(), self.params[i].grad.data_ptr()) for i in live)
+        if key != self._key:
+            self._build_table(live)
+            self._key = key
+        self.steps += 1
+        b = self._binding
+        with b.device_guard(self._table):
+            rc = b.lib().lora_adamw_clip_step(
+                ctypes.c_void_p(self._table.data_ptr()), len(live), self._n_chunks, float(self.lr if lr is None else lr),
+                float(self.betas[0]), float(self.betas[1]), float(self.eps), float(self.weight_decay), self.steps,
+                float(self.max_grad_norm or 0.0), ctypes.c_void_p(self._scratch.data_ptr()),
+                ctypes.c_void_p(b._stream(self.device)))
+        b._check(rc, "lora_adamw_clip_step")
+        return self._scratch[0]
+
+    def zero_grad(self, set_to_none=True):
+        for p in self.params:
+            if set_to_none:
+                p.grad = None
+            elif p.grad is not None:
+                p.grad.zero_()
+
+
 class Trainer:
     """Minimal stand-in for transformers.Trainer on this path (model(**batch) -> loss, backward,
     accumulate, reduce, clip, AdamW, linear decay)."""
@@ -109,8 +178,16 @@ class Trainer:
         self.model = model
         self.cfg = cfg
         self.params = trainable_parameters(model)
-        self.opt = torch.optim.AdamW(self.params, lr=cfg.lr, betas=cfg.betas, eps=cfg.eps,
-                                     weight_decay=cfg.weight_decay)
+        # On CUDA the clip + AdamW pair runs as two launches of this library (FusedAdamW); elsewhere (the CPU tests,
+        # the oracle runs) torch's own optimiser.
+        self.fused = bool(cfg.fused_optimizer) and all(p.is_cuda and p.dtype == torch.float32 for p in self.params)
+        if self.fused:
+            self.opt = FusedAdamW(self.params, lr=cfg.lr, betas=cfg.betas, eps=cfg.eps, weight_decay=cfg.weight_decay,
+                                  max_grad_norm=cfg.max_grad_norm)
+        else:
+            self.opt = torch.optim.AdamW(self.params, lr=cfg.lr, betas=cfg.betas, eps=cfg.eps,
+                                         weight_decay=cfg.weight_decay)
+        self._lr_fn = None
         self.sched = None
         self.global_step = 0
         self.on_step_end = on_step_end
@@ -122,7 +199,8 @@ class Trainer:
                 fn = lambda s: 1.0
             else:
                 fn = lambda s: max(0.0, (total - s) / max(1, total))
-            self.sched = torch.optim.lr_scheduler.LambdaLR(self.opt, fn)
+            self._lr_fn = fn
+            self.sched = True if self.fused else torch.optim.lr_scheduler.LambdaLR(self.opt, fn)
 
     def micro_step(self, batch: Dict, sync: bool) -> torch.Tensor:
         ctx = contextlib.nullcontext()
@@ -136,9 +214,13 @@ class Trainer:
         return loss.detach()
 
     def optimizer_step(self):
-        torch.nn.utils.clip_grad_norm_(self.params, self.cfg.max_grad_norm)
-        self.opt.step()
-        self.sched.step()
+        if self.fused:
+            # LambdaLR semantics: the k-th step (k = 0, 1, ...) runs at lr * fn(k)
+            self.last_grad_norm = self.opt.step(lr=self.cfg.lr * self._lr_fn(self.global_step))
+        else:
+            self.last_grad_norm = torch.nn.utils.clip_grad_norm_(self.params, self.cfg.max_grad_norm)
+            self.opt.step()
+            self.sched.step()
         self.opt.zero_grad(set_to_none=True)
         self.global_step += 1
 
