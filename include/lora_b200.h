@@ -206,16 +206,16 @@ int lora_act_bwd(const void* dY, const void* ZorY, void* dZ, int64_t n_elems, in
  * max_grad_norm 1.0; finetune_lora_opt_pp.py:193-197), same formulas: coef = min(1, max_norm / (norm + 1e-6)),
  * g *= coef (stored back), p *= 1 - lr wd, m = b1 m + (1-b1) g, v = b2 v + (1-b2) g^2,
  * p -= lr / (1 - b1^step) * m / (sqrt(v) / sqrt(1 - b2^step) + eps).
- * `table` is a DEVICE array of n_tensors rows of six 64-bit words {param ptr, grad ptr, exp_avg ptr, exp_avg_sq ptr,
- * element count, first chunk} (all tensors fp32, contiguous; first chunk = sum over earlier rows of
- * ceil(count / LORA_ADAMW_CHUNK)); n_chunks is that sum over all rows.  `scratch`: 4 + n_chunks floats, zeroed once
- * by the caller; after the call scratch[0] holds the gradient norm before clipping, scratch[1] the clip factor.
- * step counts from 1.  max_grad_norm <= 0 disables clipping.
+ * `table` is a DEVICE array of n_tensors rows of seven 64-bit words {param ptr, grad ptr, exp_avg ptr, exp_avg_sq ptr,
+ * element count, first chunk, ptr to the tensor's int32 step counter} (all tensors fp32, contiguous; first chunk =
+ * sum over earlier rows of ceil(count / LORA_ADAMW_CHUNK)); n_chunks is that sum over all rows.  Step counters live
+ * on the device, start at 0 and are advanced by the call, one per tensor as in torch.optim.AdamW (a tensor left out
+ * of a call keeps its count).  `scratch`: 4 + n_chunks floats, zeroed once by the caller; after the call scratch[0]
+ * holds the gradient norm before clipping, scratch[1] the clip factor.  max_grad_norm <= 0 disables clipping.
  */
 #define LORA_ADAMW_CHUNK 4096
 int lora_adamw_clip_step(const void* table, int32_t n_tensors, int64_t n_chunks, float lr, float beta1, float beta2,
-                         float eps, float weight_decay, int32_t step, float max_grad_norm, float* scratch,
-                         cudaStream_t stream);
+                         float eps, float weight_decay, float max_grad_norm, float* scratch, cudaStream_t stream);
 
 /*
  * The path's one exchange step under DDP: average the flat fp32 adapter-gradient bucket (dA|dB of every

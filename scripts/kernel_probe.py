@@ -71,6 +71,11 @@ for p in (0.05, 0.0):
         assert rc == 0, bind.last_error()
 
     tag = f"p{p}"
+    if os.environ.get("PROBE_ONLY") == "once":  # one forward + backward per dropout setting (the ncu capture target)
+        fwd(1)
+        bwd(1)
+        torch.cuda.synchronize()
+        continue
     if os.environ.get("PROBE_ONLY") == "skinny":  # fast A/B of the HBM-bound kernels
         for name, mask, fn in (("fwd_rowproj", bind.PHASE_ROWPROJ, fwd), ("bwd_rowproj", bind.PHASE_ROWPROJ, bwd),
                                ("colproj", bind.PHASE_COLPROJ, bwd)):

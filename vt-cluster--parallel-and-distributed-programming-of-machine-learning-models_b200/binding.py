@@ -63,8 +63,8 @@ _SIGNATURES = {
     "lora_ce_fwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int32, c_void_p]),
     "lora_ce_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64,
                             c_int32, c_void_p]),
-    "lora_adamw_clip_step": (c_int, [c_void_p, c_int32, c_int64, c_float, c_float, c_float, c_float, c_float, c_int32,
-                                     c_float, c_void_p, c_void_p]),
+    "lora_adamw_clip_step": (c_int, [c_void_p, c_int32, c_int64, c_float, c_float, c_float, c_float, c_float, c_float,
+                                     c_void_p, c_void_p]),
     "lora_debug_set_phase_mask": (None, [c_int32]),
     "lora_dropout_keep_mask": (c_int, [c_void_p, c_int64, c_int64, c_float, c_uint64, c_uint64, c_void_p]),
 }

@@ -939,22 +939,18 @@ int lora_bucket_allreduce_avg(float* bucket, int64_t n, void* const* syms, int32
 }
 
 int lora_adamw_clip_step(const void* table, int32_t n_tensors, int64_t n_chunks, float lr, float beta1, float beta2,
-                         float eps, float weight_decay, int32_t step, float max_grad_norm, float* scratch,
-                         cudaStream_t stream) {
+                         float eps, float weight_decay, float max_grad_norm, float* scratch, cudaStream_t stream) {
   g_err.clear();
-  static_assert(sizeof(optim::TensorEntry) == 6 * sizeof(int64_t), "table row = six 64-bit words");
+  static_assert(sizeof(optim::TensorEntry) == 7 * sizeof(int64_t), "table row = seven 64-bit words");
   static_assert(optim::CHUNK == LORA_ADAMW_CHUNK, "chunk size");
   if (!table || !scratch) return fail("lora_adamw_clip_step: null pointer argument");
   if (n_tensors < 1 || n_chunks < n_tensors || n_chunks > INT32_MAX) return fail("lora_adamw_clip_step: bad tensor / chunk counts");
-  if (step < 1) return fail("lora_adamw_clip_step: step counts from 1");
   if (!(beta1 >= 0.f && beta1 < 1.f && beta2 >= 0.f && beta2 < 1.f)) return fail("lora_adamw_clip_step: betas must be in [0, 1)");
-  const float bc1 = 1.f - std::pow(beta1, static_cast<float>(step));
-  const float bc2s = std::sqrt(1.f - std::pow(beta2, static_cast<float>(step)));
   const optim::TensorEntry* tab = static_cast<const optim::TensorEntry*>(table);
   CUDA_TRY(launch_pdl(optim::sumsq_kernel, dim3((unsigned)n_chunks), dim3(optim::THREADS), 0, stream, 1, tab, (int)n_tensors,
                       (long long)n_chunks, max_grad_norm, scratch));
   CUDA_TRY(launch_pdl(optim::adamw_kernel, dim3((unsigned)n_chunks), dim3(optim::THREADS), 0, stream, 1, tab, (int)n_tensors,
-                      (const float*)scratch, lr, beta1, beta2, eps, weight_decay, bc1, bc2s));
+                      (const float*)scratch, lr, beta1, beta2, eps, weight_decay));
   return 0;
 }
 

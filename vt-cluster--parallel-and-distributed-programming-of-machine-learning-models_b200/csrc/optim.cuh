@@ -24,6 +24,8 @@ struct TensorEntry {  // one adapter tensor (all fp32, contiguous)
   float* v;
   long long n;
   long long first_chunk;  // prefix sum of ceil(n / CHUNK) over the tensors before this one
+  int* step;              // this tensor's own step count (torch.optim.AdamW keeps one per parameter: a tensor that
+                          // had no gradient in some step lags behind); advanced here, on the device
 };
 
 // scratch layout (floats): [0] norm, [1] coef, [2] arrival counter (as uint), [4 ...] per-chunk partial sums
@@ -82,12 +84,13 @@ __global__ void __launch_bounds__(THREADS)
       scratch[0] = norm;
       scratch[1] = max_norm > 0.f ? fminf(1.f, max_norm / (norm + 1e-6f)) : 1.f;
     }
+    for (int t = threadIdx.x; t < n_tensors; t += THREADS) *tab[t].step += 1;  // read by adamw_kernel (next launch)
   }
 }
 
 __global__ void __launch_bounds__(THREADS)
     adamw_kernel(const TensorEntry* __restrict__ tab, int n_tensors, const float* __restrict__ scratch, float lr,
-                 float beta1, float beta2, float eps, float weight_decay, float bias_c1, float bias_c2_sqrt) {
+                 float beta1, float beta2, float eps, float weight_decay) {
   pdl_launch_dependents();
   pdl_wait();
   const long long chunk = blockIdx.x;
@@ -95,6 +98,8 @@ __global__ void __launch_bounds__(THREADS)
   const long long base = (chunk - e.first_chunk) * CHUNK;
   const long long end = min(e.n, base + CHUNK);
   const float coef = scratch[1];
+  const float t = static_cast<float>(*e.step);  // >= 1: sumsq_kernel advanced it
+  const float bias_c1 = 1.f - powf(beta1, t), bias_c2_sqrt = sqrtf(1.f - powf(beta2, t));
   const float step = lr / bias_c1;
   const float decay = 1.f - lr * weight_decay;
   for (long long i = base + threadIdx.x; i < end; i += THREADS) {

@@ -116,7 +116,7 @@ class FusedAdamW:
         self.device = self.params[0].device
         self.exp_avg = [torch.zeros_like(p) for p in self.params]
         self.exp_avg_sq = [torch.zeros_like(p) for p in self.params]
-        self.steps = 0
+        self._steps = torch.zeros(len(self.params), dtype=torch.int32, device=self.device)  # per tensor, as torch keeps them
         self._binding = binding
         self._key, self._table, self._n_chunks, self._scratch = None, None, 0, None
 
@@ -126,7 +126,7 @@ class FusedAdamW:
         for i in live:
             p = self.params[i]
             rows.append([p.data_ptr(), p.grad.data_ptr(), self.exp_avg[i].data_ptr(), self.exp_avg_sq[i].data_ptr(),
-                         p.numel(), first])
+                         p.numel(), first, self._steps.data_ptr() + 4 * i])
             first += (p.numel() + chunk - 1) // chunk
         self._table = torch.tensor(rows, dtype=torch.int64).to(self.device)
         if self._scratch is None or self._scratch.numel() < 4 + first:
@@ -149,12 +149,11 @@ class FusedAdamW:
         if key != self._key:
             self._build_table(live)
             self._key = key
-        self.steps += 1
         b = self._binding
         with b.device_guard(self._table):
             rc = b.lib().lora_adamw_clip_step(
                 ctypes.c_void_p(self._table.data_ptr()), len(live), self._n_chunks, float(self.lr if lr is None else lr),
-                float(self.betas[0]), float(self.betas[1]), float(self.eps), float(self.weight_decay), self.steps,
+                float(self.betas[0]), float(self.betas[1]), float(self.eps), float(self.weight_decay),
                 float(self.max_grad_norm or 0.0), ctypes.c_void_p(self._scratch.data_ptr()),
                 ctypes.c_void_p(b._stream(self.device)))
         b._check(rc, "lora_adamw_clip_step")
