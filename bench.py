@@ -919,7 +919,10 @@ def main():
         import torch.distributed as dist
 
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=device)
+        import datetime
+
+        dist.init_process_group("nccl", device_id=device,
+                                timeout=datetime.timedelta(seconds=int(os.environ.get("LORA_B200_DIST_TIMEOUT_S", "600"))))
     try:
         if a.workload == "opt27b_pp":
             line = run_pipeline(a, pkg, rank, world, device)

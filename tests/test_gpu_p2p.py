@@ -2,6 +2,7 @@
 box: against the fp64 mean of the per-rank inputs (which every rank can regenerate), bit-identical across
 ranks, many calls in a row (parity reuse), one-shot / two-shot / ragged sizes, and as a DDP comm hook
 against torch's own NCCL all-reduce.  Skipped where only one GPU is visible."""
+import datetime
 import os
 import sys
 
@@ -23,7 +24,7 @@ def _worker(rank, world, port, q):
         pkg = g.load_package()
         torch.cuda.set_device(rank)
         dev = torch.device("cuda", rank)
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev, timeout=datetime.timedelta(seconds=120))
         ex = pkg.comm.PeerBucketExchange(1 << 20)
 
         def data(r, step, n):
@@ -82,7 +83,7 @@ def test_peer_bucket_exchange_two_or_more_gpus():
     procs = [ctx.Process(target=_worker, args=(r, world, 29611, q)) for r in range(world)]
     for p in procs:
         p.start()
-    res = [q.get(timeout=540) for _ in procs]
+    res = [q.get(timeout=300) for _ in procs]
     for p in procs:
         p.join(60)
     assert all(r[1] == "ok" for r in res), res

@@ -4,6 +4,7 @@ re-ordering, so loss, clip norm and every adapter gradient must equal those of t
 over the same micro-batches (fp16, BASELINE.json configs[4]; LoRA dropout off: split and unsplit models draw from
 different generators).  Runs 2, 4 and 8 stages as far as the box has GPUs; skipped with fewer than two.
 Reference intent: finetune_lora_opt_pp.py:156 (split), :121-153 (stage wrappers), :213-224 (train_batch)."""
+import datetime
 import os
 import socket
 import sys
@@ -55,7 +56,7 @@ def _worker(rank, world, port, q, overlap):
         pkg = g.load_package()
         torch.cuda.set_device(rank)
         dev = torch.device("cuda", rank)
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev, timeout=datetime.timedelta(seconds=120))
         batches = pkg.train.synthetic_batches(N_MICRO, batch=2, seq=64, vocab=512, pad_id=1, seed=77, device=dev)
         pm = _model(pkg, dev)
         stage = pkg.pipeline.OPTStage(pm.base_model.model, rank, world)
@@ -120,7 +121,7 @@ def test_pipeline_on_gpus_equals_unsplit_model(world, overlap):
     procs = [ctx.Process(target=_worker, args=(r, world, port, q, overlap)) for r in range(world)]
     for p in procs:
         p.start()
-    res = [q.get(timeout=600) for _ in procs]
+    res = [q.get(timeout=300) for _ in procs]
     for p in procs:
         p.join(60)
     assert all(r[1] == "ok" for r in res), res
