@@ -551,7 +551,76 @@ def run_point(a, pkg, rank, world, device, with_e2e=True, with_kernels=True, wit
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             e2e_ms = float(t.item())
         e2e = {"value": world * M / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": (M * K + M * N) * esz,
-               "d2h_bytes_per_step": (M * N + M * K) * esz + (r * K + N * r) * 4, "ms_per_step": e2e_ms}
+               "d2h_bytes_per_step": (M * N + M * K) * esz + (r * K + N * r) * 4, "ms_per_step": e2e_ms,
+               "copies": "serial: H2D, compute, D2H on one stream"}
+
+        # The same step with the copies of consecutive steps overlapped, as an input pipeline would run it: step
+        # i+1's H2D (copy stream) and step i-1's D2H (second copy stream) run under step i's compute; every step still
+        # moves its own inputs in and its own results out inside the timed region (PCIe is full duplex).
+        s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+        slots = [{"x": torch.empty(M, K, dtype=dtype, device=device), "dy": torch.empty(M, N, dtype=dtype, device=device),
+                  "in": torch.cuda.Event(), "done": torch.cuda.Event(), "out": torch.cuda.Event(), "keep": None}
+                 for _ in range(2)]
+        hys = [hy, torch.empty_like(hy).pin_memory()]
+        hdxs = [hdx, torch.empty_like(hdx).pin_memory()]
+
+        def stage_in(i):
+            sl = slots[i & 1]
+            with torch.cuda.stream(s_in):
+                s_in.wait_event(sl["out"])  # the slot's previous results have left the device
+                sl["x"].copy_(hx, non_blocking=True)
+                sl["dy"].copy_(hdy, non_blocking=True)
+                sl["in"].record(s_in)
+
+        def piped_step(i, prefetch=True):
+            sl = slots[i & 1]
+            cur = torch.cuda.current_stream()
+            cur.wait_event(sl["in"])
+            if prefetch:
+                stage_in(i + 1)
+            xd = sl["x"].detach().requires_grad_(True)
+            y = pkg.fused_lora_linear(xd, W, b, Ap, Bp, s, p=p, training=True, w_is_KN=a.conv1d)
+            y.backward(sl["dy"])
+            if exch is not None:
+                exch.allreduce_avg_(Ap.grad)
+                exch.allreduce_avg_(Bp.grad)
+            ga, gb = Ap.grad, Bp.grad
+            Ap.grad = Bp.grad = None
+            sl["done"].record(cur)
+            sl["keep"] = (y, xd.grad, ga, gb)  # alive until the slot's next use, two steps on
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(sl["done"])
+                hys[i & 1].copy_(y.detach(), non_blocking=True)
+                hdxs[i & 1].copy_(xd.grad, non_blocking=True)
+                hda.copy_(ga, non_blocking=True)
+                hdb.copy_(gb, non_blocking=True)
+                sl["out"].record(s_out)
+
+        for sl in slots:
+            sl["out"].record()
+        stage_in(0)
+        for i in range(3):
+            piped_step(i)
+        torch.cuda.synchronize()
+        barrier()
+        e0.record()
+        for i in range(3, 3 + e2e_steps):
+            piped_step(i, prefetch=i + 1 < 3 + e2e_steps)
+        torch.cuda.current_stream().wait_stream(s_out)  # the last step's results are on the host
+        e1.record()
+        barrier()
+        piped_ms = e0.elapsed_time(e1) / e2e_steps
+        if dist_on:
+            t = torch.tensor([piped_ms], device=device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            piped_ms = float(t.item())
+        e2e["serial_copies"] = {"value": e2e["value"], "ms_per_step": e2e_ms}
+        e2e["pipelined_copies"] = {"value": world * M / (piped_ms * 1e-3), "ms_per_step": piped_ms}
+        if piped_ms < e2e_ms:
+            e2e.update(value=world * M / (piped_ms * 1e-3), ms_per_step=piped_ms,
+                       copies="pipelined: step i+1's H2D and step i-1's D2H on copy streams under step i's compute")
+        for sl in slots:
+            sl["keep"] = None
 
         # the same public autograd call with inputs resident in HBM, launched eagerly from Python: what a training
         # script gets per layer call (`value` above is the raw C-ABI sequence replayed as one CUDA graph)
