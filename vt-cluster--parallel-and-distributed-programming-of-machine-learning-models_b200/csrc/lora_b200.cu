@@ -18,6 +18,7 @@
 #include "ce.cuh"
 #include "p2p.cuh"
 #include "gemm_sm100.cuh"
+#include "gemm_masked_sm100.cuh"
 #include "lora_b200.h"
 #include "optim.cuh"
 #include "skinny.cuh"
@@ -188,6 +189,7 @@ int device_setup(int* sm_count) {
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<true, true, false, true>, gemm::SMEM_BYTES));
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false, false, true>, gemm::SMEM_BYTES));
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false, true, true>, gemm::SMEM_BYTES));
+    CUDA_TRY(opt_in_smem(gemm::gemm_masked_kernel, gemm::SMEM_BYTES));
 #define OPT_IN_SKINNY(BF, RP)                                                                     \
   CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP>, skinny::rp_smem_bytes<RP>()));             \
   CUDA_TRY(opt_in_smem(skinny::colproj_kernel<BF, RP>, skinny::cp_smem_bytes<RP>()));
@@ -436,8 +438,56 @@ int launch_gemm_t(const CUtensorMap& tmA1, const CUtensorMap& tmB1, const CUtens
   return 0;
 }
 
+// Backward with dropout, pair mode: 256 x 128 tiles with the rank-r product in its own TMEM accumulator
+// (gemm_masked_sm100.cuh).
+int launch_gemm_masked_pair(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, int sm_count, cudaStream_t stream) {
+  const int rp = rpad_of(g.masked_r);
+  CUtensorMap tmA1, tmB1, tmA2, tmB2, tmD;
+  if (make_tmap(&tmA1, g.A1, dtype, K1, M, g.lda1 ? g.lda1 : K1, gemm::BK, gemm::BM, CU_TENSOR_MAP_SWIZZLE_128B, "masked gemm A1")) return 1;
+  if (!g.b_mn_major) {
+    if (make_tmap(&tmB1, g.B1, dtype, K1, N, K1, gemm::BK, gemm::M_B_ROWS, CU_TENSOR_MAP_SWIZZLE_128B, "masked gemm B1 (K-major)")) return 1;
+  } else {
+    if (make_tmap(&tmB1, g.B1, dtype, N, K1, N, 64, gemm::BK, CU_TENSOR_MAP_SWIZZLE_128B, "masked gemm B1 (MN-major)")) return 1;
+  }
+  const CUtensorMapSwizzle sw = swizzle_for_row_bytes(rp * 2);
+  if (make_tmap(&tmA2, g.dh, dtype, rp, M, rp, rp, gemm::BM, sw, "masked gemm dH")) return 1;
+  if (make_tmap(&tmB2, g.a16, dtype, rp, N, rp, rp, gemm::M_B_ROWS, sw, "masked gemm A^T")) return 1;
+  if (make_tmap(&tmD, g.D, dtype, N, M, g.ldd ? g.ldd : N, 64, 32, CU_TENSOR_MAP_SWIZZLE_128B, "masked gemm D")) return 1;
+  gemm::MaskedParams p;
+  p.M = (int)M;
+  p.N = (int)N;
+  p.K1 = (int)K1;
+  p.r_pad = rp;
+  p.b_mn_major = g.b_mn_major;
+  p.dtype = dtype;
+  p.keep = g.keep;
+  p.inv_keep = g.inv_keep;
+  const long long tiles = ((M + 2 * gemm::BM - 1) / (2 * gemm::BM)) * ((N + gemm::MBN - 1) / gemm::MBN);
+  const int grid = 2 * static_cast<int>(std::min<long long>(tiles, sm_count / 2));
+  CUDA_TRY(launch_pdl(gemm::gemm_masked_kernel, dim3(grid), dim3(gemm::THREADS), gemm::SMEM_BYTES, stream, 2, tmA1, tmB1, tmA2,
+                      tmB2, tmD, p));
+  return 0;
+}
+
+// Which masked flavour a pair-mode backward takes.  Measured (M = 16384, r02): the 128-column TMEM flavour costs the
+// same ~194 us at 2560 -> 2560 whatever the rank (its main loop runs at ~3/4 of the 256-column kernel's rate), the
+// epilogue flavour 165 / 180 / 288 us at r = 8 / 16 / 64; with a short contraction the epilogue flavour is bound by
+// its epilogue (dX of 3072 -> 768 over K1 = 768: 86 us against 64 us).  So: wide ranks and short contractions go
+// to the TMEM flavour.  LORA_B200_MASKED=epilogue|tmem forces one for A/B timing; both are exact implementations
+// of the same formula.
+bool use_masked_tmem(int rp, int64_t K1) {
+  static const int forced = [] {
+    const char* e = getenv("LORA_B200_MASKED");
+    return !e ? 0 : (strcmp(e, "epilogue") == 0 ? 1 : (strcmp(e, "tmem") == 0 ? 2 : 0));
+  }();
+  if (forced) return forced == 2;
+  return rp >= 32 || K1 <= 1024;
+}
+
 int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, int sm_count, cudaStream_t stream) {
   const bool pair = pair_mode_allowed() && M > gemm::BM && sm_count >= 2;
+  if (pair && g.masked_r > 0 && !g.bias && !g.act && use_masked_tmem(rpad_of(g.masked_r), K1))
+    return launch_gemm_masked_pair(g, M, N, K1, dtype, sm_count, stream);
   const uint32_t b_rows = pair ? gemm::BN / 2 : gemm::BN;  // rows of the B tile one CTA stages
   CUtensorMap tmA1, tmB1, tmA2, tmB2, tmD, tmZ;
   if (make_tmap(&tmA1, g.A1, dtype, K1, M, g.lda1 ? g.lda1 : K1, gemm::BK, gemm::BM, CU_TENSOR_MAP_SWIZZLE_128B, "gemm A1")) return 1;
