@@ -84,7 +84,7 @@ def test_static_scratch_matches_workspace_path_twice_in_a_row(pkg):
 
 def test_static_scratch_rejects_oversized_shapes(pkg):
     lib = pkg.binding.lib()
-    M, N, r = 16384, 2560, 64  # 7 row splits x 2560 x 64 x 4 B = 4.4 MiB > the 4 MiB block
+    M, N, r = 256, 20480, 64  # one row split x 20480 x 64 x 4 B = 5 MiB of partial sums > the 4 MiB block
     dy = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
     H = torch.zeros(M, 64, dtype=torch.bfloat16, device="cuda")
     dB = torch.zeros(N, r, device="cuda")

@@ -213,13 +213,12 @@ struct Split {
 // Row splits of the column projections; sized for 148 SMs on purpose so that
 // the workspace size does not depend on the device queried.
 // `launch_tiles` = column tiles of ALL problems that share the launch (dB and dA go together).
-Split colproj_split(int64_t M, int64_t launch_tiles) {
+Split colproj_split(int64_t M, int64_t launch_tiles, int rp) {
   const int64_t m_tiles = (M + skinny::CP_BM - 1) / skinny::CP_BM;
-  // two CTAs fit per SM: aim for at most one full wave (2*148 CTAs) so that no straggler wave forms
-#ifndef LB_EXP_CP_SLOTS
-#define LB_EXP_CP_SLOTS (2 * 148)
-#endif
-  int64_t want = LB_EXP_CP_SLOTS / launch_tiles;
+  // aim for at most one full wave so that no straggler wave forms: two CTAs fit per SM at padded rank 16, one at
+  // 32 / 64 (128 / 168 registers); fewer, longer CTAs also amortise the per-CTA reduction and fold, which at r = 64
+  // outweighed the streaming (768 -> 768: 110 us with 12 row splits)
+  int64_t want = ((rp <= 16 ? 2 : 1) * 148) / launch_tiles;
   if (want < 1) want = 1;
   if (want > m_tiles) want = m_tiles;
   const int64_t tiles_per = (m_tiles + want - 1) / want;
@@ -257,7 +256,7 @@ Workspace carve(int64_t M, int64_t K, int64_t N, int r) {
   size_t off = 0;
   w.dh = off;    off += align256(static_cast<size_t>(M) * rp * 2);
   w.counters = off; off += align256(2 * kMaxColTiles * sizeof(unsigned int));
-  const Split sp = colproj_split(M, colproj_tiles(K, rp) + colproj_tiles(N, rp));
+  const Split sp = colproj_split(M, colproj_tiles(K, rp) + colproj_tiles(N, rp), rp);
   const size_t pk = static_cast<size_t>(sp.splits) * K * rp * 4, pn = static_cast<size_t>(sp.splits) * N * rp * 4;
   w.partial = off;  off += align256(pn);   // dB partial sums
   w.partial2 = off; off += align256(pk);   // dA partial sums (both column projections share one launch)
@@ -366,7 +365,7 @@ int launch_colproj(const ColProjJob* jobs, int njobs, int64_t M, int r, int rp, 
   skinny::ColProjParams pp{};
   int64_t launch_tiles = 0;
   for (int i = 0; i < njobs; ++i) launch_tiles += colproj_tiles(jobs[i].C, rp);
-  const Split sp = colproj_split(M, launch_tiles);
+  const Split sp = colproj_split(M, launch_tiles, rp);
   for (int i = 0; i < 2; ++i) {
     const ColProjJob& j = jobs[i < njobs ? i : 0];
     if (make_tmap(&tmAct[i], j.act, dtype, j.C, M, j.C, 64, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_128B, "colproj act")) return 1;
@@ -760,7 +759,7 @@ int lora_linear_grad_b_static(const void* dY, const void* H, float* dB, int64_t 
   if (dtype != kDtypeBf16 && dtype != kDtypeFp16) return fail("lora_linear_grad_b_static: dtype must be 0 (bf16) or 1 (fp16)");
   if (!dY || !H || !dB) return fail("lora_linear_grad_b_static: null pointer argument");
   const int rp = rpad_of(r);
-  const Split sp = colproj_split(M, colproj_tiles(N, rp));
+  const Split sp = colproj_split(M, colproj_tiles(N, rp), rp);
   const size_t counter_bytes = align256(kMaxColTiles * sizeof(unsigned int));
   const size_t need = counter_bytes + static_cast<size_t>(sp.splits) * static_cast<size_t>(N) * rp * sizeof(float);
   if (need > static_cast<size_t>(LORA_B200_STATIC_SCRATCH_BYTES))
