@@ -218,7 +218,17 @@ Split colproj_split(int64_t M, int64_t launch_tiles, int rp) {
   // aim for at most one full wave so that no straggler wave forms: two CTAs fit per SM at padded rank 16, one at
   // 32 / 64 (128 / 168 registers); fewer, longer CTAs also amortise the per-CTA reduction and fold, which at r = 64
   // outweighed the streaming (768 -> 768: 110 us with 12 row splits)
-  int64_t want = ((rp <= 16 ? 2 : 1) * 148) / launch_tiles;
+  int64_t want = (2 * 148) / launch_tiles;
+  if (rp > 16) {  // one CTA per SM: the split count (<= 8) with the fewest CTA-waves per unit of work, ties to the smaller
+    double best = 1e30;
+    for (int64_t sct = 1; sct <= 8; ++sct) {
+      const double cost = static_cast<double>((launch_tiles * sct + 147) / 148) / static_cast<double>(sct);
+      if (cost < best - 1e-9) {
+        best = cost;
+        want = sct;
+      }
+    }
+  }
   if (want < 1) want = 1;
   if (want > m_tiles) want = m_tiles;
   const int64_t tiles_per = (m_tiles + want - 1) / want;
@@ -369,7 +379,8 @@ int launch_colproj(const ColProjJob* jobs, int njobs, int64_t M, int r, int rp, 
   for (int i = 0; i < 2; ++i) {
     const ColProjJob& j = jobs[i < njobs ? i : 0];
     if (make_tmap(&tmAct[i], j.act, dtype, j.C, M, j.C, 64, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_128B, "colproj act")) return 1;
-    if (make_tmap(&tmSmall[i], j.small, dtype, rp, M, rp, rp, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_NONE, "colproj small")) return 1;
+    const CUtensorMapSwizzle ssw = rp == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : (rp == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE);
+    if (make_tmap(&tmSmall[i], j.small, dtype, rp, M, rp, rp, skinny::CP_BM, ssw, "colproj small")) return 1;
     skinny::ColProjProblem& q = pp.prob[i];
     q.partial = j.partial;
     q.counters = j.counters;

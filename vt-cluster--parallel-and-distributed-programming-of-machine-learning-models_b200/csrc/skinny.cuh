@@ -520,7 +520,10 @@ __global__ void __launch_bounds__(CP_THREADS, cp_min_ctas(kRPad))
 #pragma unroll
         for (int n = 0; n < NB; ++n) {
           const int mrow = warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
-          ldsm_x2_t(sm_u + mrow * SROW + n * 16, b[n]);
+          // rows of 64 / 128 bytes are stored TMA-swizzled (16-byte chunk index XOR row bits): unswizzled, the eight
+          // row addresses of an ldmatrix fall into the same banks (8-way conflict at r_pad = 64)
+          const int chunk = kRPad == 64 ? (n ^ (mrow & 7)) : (kRPad == 32 ? (n ^ ((mrow >> 1) & 3)) : n);
+          ldsm_x2_t(sm_u + mrow * SROW + chunk * 16, b[n]);
         }
         if (warp * 16 + 16 > valid_rows) {
           // Partially valid 16-row slab: zero B-fragment entries of dead rows.
