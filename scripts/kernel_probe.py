@@ -77,7 +77,7 @@ for p in (0.05, 0.0):
         torch.cuda.synchronize()
         continue
     if os.environ.get("PROBE_ONLY") == "skinny":  # fast A/B of the HBM-bound kernels
-        for name, mask, fn in (("fwd_rowproj", bind.PHASE_ROWPROJ, fwd), ("bwd_rowproj", bind.PHASE_ROWPROJ, bwd),
+        for name, mask, fn in (("fwd_rowproj", bind.PHASE_ROWPROJ | bind.PHASE_PACK, fwd), ("bwd_rowproj", bind.PHASE_ROWPROJ, bwd),
                                ("colproj", bind.PHASE_COLPROJ, bwd)):
             bind.set_phase_mask(mask)
             try:
@@ -86,8 +86,8 @@ for p in (0.05, 0.0):
                 bind.set_phase_mask(bind.PHASE_ALL)
         continue
     for name, mask, fn in (("fwd_gemm", bind.PHASE_GEMM, fwd), ("bwd_gemm", bind.PHASE_GEMM, bwd),
-                           ("fwd_rowproj", bind.PHASE_ROWPROJ, fwd), ("bwd_rowproj", bind.PHASE_ROWPROJ, bwd),
-                           ("colproj", bind.PHASE_COLPROJ, bwd), ("pack", bind.PHASE_PACK, fwd)):
+                           ("fwd_rowproj", bind.PHASE_ROWPROJ | bind.PHASE_PACK, fwd), ("bwd_rowproj", bind.PHASE_ROWPROJ, bwd),
+                           ("colproj", bind.PHASE_COLPROJ, bwd)):
         bind.set_phase_mask(mask)
         try:
             out[f"{name}_us_{tag}"] = timeit(fn)

@@ -193,6 +193,10 @@ int device_setup(int* sm_count) {
 #define OPT_IN_SKINNY(BF, RP)                                                                     \
   CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP>, skinny::rp_smem_bytes<RP>()));             \
   CUDA_TRY(opt_in_smem(skinny::colproj_kernel<BF, RP>, skinny::cp_smem_bytes<RP>()));
+    CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<true, 16, true, 1>, skinny::rp_smem_bytes<16>()));
+    CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<false, 16, true, 1>, skinny::rp_smem_bytes<16>()));
+    CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<true, 16, true, 2>, skinny::rp_smem_bytes<16>()));
+    CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<false, 16, true, 2>, skinny::rp_smem_bytes<16>()));
     OPT_IN_SKINNY(true, 16) OPT_IN_SKINNY(true, 32) OPT_IN_SKINNY(true, 64)
     OPT_IN_SKINNY(false, 16) OPT_IN_SKINNY(false, 32) OPT_IN_SKINNY(false, 64)
 #undef OPT_IN_SKINNY
@@ -300,24 +304,38 @@ int launch_pack(const float* A, const float* B, uint8_t* pk, const Packed& w, in
   return 0;
 }
 
-template <bool BF, int RP>
+template <bool BF, int RP, bool DIRECT = false, int NBE = 2>
 int launch_rowproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmP, const skinny::RowProjParams& p,
                      cudaStream_t stream) {
   const int grid = (p.M + skinny::rp_rows(RP) - 1) / skinny::rp_rows(RP);
-  CUDA_TRY(launch_pdl(skinny::rowproj_kernel<BF, RP>, dim3(grid), dim3(skinny::rp_threads(RP)), skinny::rp_smem_bytes<RP>(),
-                      stream, 1, tmAct, tmP, p));
+  CUDA_TRY(launch_pdl(skinny::rowproj_kernel<BF, RP, DIRECT, NBE>, dim3(grid), dim3(skinny::rp_threads(RP)),
+                      skinny::rp_smem_bytes<RP>(), stream, 1, tmAct, tmP, p));
   return 0;
 }
+
+// Forward with padded rank 16 and the fp32 masters at hand: the row projection reads A directly and packs A, B
+// for the kernels after it (no separate pack launch).
+struct DirectPack {
+  const float* A = nullptr;
+  const float* B = nullptr;
+  int r = 0;
+  int64_t N = 0;
+  float s = 0.f;
+  uint8_t* pk = nullptr;
+  const Packed* w = nullptr;
+};
 
 // out[M, rp] = out_scale * (keep .* act)[M, C] * P[rp, C]^T; with p > 0 the keep-bits are drawn here and stored.
 // zero_words: optional block of words the kernel clears (arrival counters of the column projections).
 int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out, int64_t M, int64_t C, int rp, int dtype,
                    float out_scale, float p, uint64_t seed, uint64_t offset, cudaStream_t stream,
-                   const uint64_t* offset_dev = nullptr, unsigned int* zero_words = nullptr, int n_zero_words = 0) {
+                   const uint64_t* offset_dev = nullptr, unsigned int* zero_words = nullptr, int n_zero_words = 0,
+                   const DirectPack* direct = nullptr) {
   CUtensorMap tmAct, tmP;
   if (make_tmap(&tmAct, act, dtype, C, M, C, skinny::RP_BK, skinny::rp_rows(rp), CU_TENSOR_MAP_SWIZZLE_128B, "rowproj act")) return 1;
-  if (make_tmap(&tmP, P, dtype, C, rp, C, skinny::RP_BK, rp, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj P")) return 1;
-  skinny::RowProjParams rp_p;
+  if (direct) tmP = tmAct;  // unused by the direct-A kernel
+  else if (make_tmap(&tmP, P, dtype, C, rp, C, skinny::RP_BK, rp, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj P")) return 1;
+  skinny::RowProjParams rp_p{};
   rp_p.out = out;
   rp_p.keep_out = keep_out;
   rp_p.M = (int)M;
@@ -331,6 +349,22 @@ int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out,
   rp_p.zero_words = zero_words;
   rp_p.n_zero_words = n_zero_words;
   const bool bf = dtype == kDtypeBf16;
+  if (direct) {
+    rp_p.A32 = direct->A;
+    rp_p.B32 = direct->B;
+    rp_p.r = direct->r;
+    rp_p.N = (int)direct->N;
+    rp_p.s = direct->s;
+    rp_p.a16 = direct->pk + direct->w->a16;
+    rp_p.a16t = direct->pk + direct->w->a16t;
+    rp_p.sb16 = direct->pk + direct->w->sb16;
+    rp_p.sb16t = direct->pk + direct->w->sb16t;
+    if (direct->r <= 8)
+      return bf ? launch_rowproj_t<true, 16, true, 1>(tmAct, tmP, rp_p, stream)
+                : launch_rowproj_t<false, 16, true, 1>(tmAct, tmP, rp_p, stream);
+    return bf ? launch_rowproj_t<true, 16, true, 2>(tmAct, tmP, rp_p, stream)
+              : launch_rowproj_t<false, 16, true, 2>(tmAct, tmP, rp_p, stream);
+  }
 #define RP_CASE(BF, RP) return launch_rowproj_t<BF, RP>(tmAct, tmP, rp_p, stream);
   if (bf) {
     if (rp == 16) RP_CASE(true, 16) else if (rp == 32) RP_CASE(true, 32) else RP_CASE(true, 64)
@@ -665,10 +699,23 @@ int lora_linear_fwd_devrng(const void* X, const void* W, const void* bias, const
   const int rp = rpad_of(r);
   const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
 
-  if (A != nullptr && phase_on(kPhasePack) && launch_pack(A, B, pk, w, K, N, r, scaling, dtype, stream)) return 1;
-  if (phase_on(kPhaseRowProj) &&
-      launch_rowproj(X, pk + w.a16, H, keep_mask, M, K, rp, dtype, inv_keep, p, seed, offset, stream, offset_dev))
-    return 1;
+  // Padded rank 16 (every adapter of the reference) with the masters at hand: the row projection reads A itself and
+  // does the pack as a side job -- two launches per forward.  Wider ranks (or A = B = NULL) keep the pack launch.
+  const bool direct = A != nullptr && rp == 16 && phase_on(kPhaseRowProj) && phase_on(kPhasePack);
+  if (A != nullptr && !direct && phase_on(kPhasePack) && launch_pack(A, B, pk, w, K, N, r, scaling, dtype, stream)) return 1;
+  if (phase_on(kPhaseRowProj)) {
+    DirectPack dp;
+    dp.A = A;
+    dp.B = B;
+    dp.r = r;
+    dp.N = N;
+    dp.s = scaling;
+    dp.pk = pk;
+    dp.w = &w;
+    if (launch_rowproj(X, pk + w.a16, H, keep_mask, M, K, rp, dtype, inv_keep, p, seed, offset, stream, offset_dev, nullptr, 0,
+                       direct ? &dp : nullptr))
+      return 1;
+  }
   if (!phase_on(kPhaseGemm)) return 0;
   GemmArgs g{};
   g.A1 = X;

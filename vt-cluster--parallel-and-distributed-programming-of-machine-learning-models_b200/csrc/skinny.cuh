@@ -11,6 +11,8 @@
 // dropout acts on the adapter input only, scaling = lora_alpha / r.
 #pragma once
 
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace lb {
@@ -69,15 +71,12 @@ __device__ __forceinline__ __half cvt16<__half>(float v) {
 }
 
 template <typename T>
-__global__ void pack_adapters_kernel(const float* __restrict__ A, const float* __restrict__ B, T* __restrict__ a16,
-                                     T* __restrict__ a16t, T* __restrict__ sb16, T* __restrict__ sb16t, int K, int N,
-                                     int r, int r_pad, float s) {
-  pdl_launch_dependents();
-  pdl_wait();  // the block may still be read by kernels of an earlier call on this stream
+__device__ __forceinline__ void pack_adapters_body(const float* __restrict__ A, const float* __restrict__ B, T* __restrict__ a16,
+                                                   T* __restrict__ a16t, T* __restrict__ sb16, T* __restrict__ sb16t, int K,
+                                                   int N, int r, int r_pad, float s, long long first, long long stride) {
   const long long na = static_cast<long long>(r_pad) * K;
   const long long nb = static_cast<long long>(N) * r_pad;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < na + nb;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+  for (long long i = first; i < na + nb; i += stride) {
     if (i < na) {
       const int j = static_cast<int>(i / K), k = static_cast<int>(i % K);
       const T v = cvt16<T>(j < r ? A[static_cast<long long>(j) * K + k] : 0.f);
@@ -91,6 +90,17 @@ __global__ void pack_adapters_kernel(const float* __restrict__ A, const float* _
       sb16t[static_cast<long long>(j) * N + n] = v;
     }
   }
+}
+
+template <typename T>
+__global__ void pack_adapters_kernel(const float* __restrict__ A, const float* __restrict__ B, T* __restrict__ a16,
+                                     T* __restrict__ a16t, T* __restrict__ sb16, T* __restrict__ sb16t, int K, int N,
+                                     int r, int r_pad, float s) {
+  pdl_launch_dependents();
+  pdl_wait();  // the block may still be read by kernels of an earlier call on this stream
+  pack_adapters_body<T>(A, B, a16, a16t, sb16, sb16t, K, N, r, r_pad, s,
+                        blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x,
+                        static_cast<long long>(gridDim.x) * blockDim.x);
 }
 
 // ---------------------------------------------------------------------------
@@ -144,12 +154,21 @@ struct RowProjParams {
   uint32_t thresh14;  // round(p * 16384)
   unsigned int* zero_words;  // optional: words CTA 0 clears (the column projections' arrival counters)
   int n_zero_words;
+  // kDirectA (forward, padded rank 16): the projection matrix is read straight from the fp32 master A [r, C]
+  // and the kernel also does the pack (A, B -> the four 16-bit layouts) as a side job for the kernels that follow,
+  // so the forward needs no pack launch.
+  const float* A32;
+  const float* B32;  // [N, r]
+  int r, N;
+  float s;           // scaling folded into the packed B
+  void *a16, *a16t, *sb16, *sb16t;
 };
 
-template <bool kBf16, int kRPad>
+template <bool kBf16, int kRPad, bool kDirectA = false, int kNBE = 2>
 __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
     rowproj_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constant__ CUtensorMap tmP,
                    const RowProjParams p) {
+  static_assert(!kDirectA || kRPad == 16, "the direct-A path holds its B fragments in registers: padded rank 16 only");
   constexpr int SLOT = rp_slot_bytes<kRPad>();
   constexpr int NB = kRPad / 8;
   constexpr int SLABS = rp_slabs(kRPad);
@@ -180,6 +199,14 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
   // this only covers a workspace that has never been used (or a call that was cut short).
   if (blockIdx.x == 0 && p.zero_words != nullptr)
     for (int i = threadIdx.x; i < p.n_zero_words; i += blockDim.x) p.zero_words[i] = 0u;
+  if constexpr (kDirectA) {
+    // the pack, spread over every thread of the grid (a few elements each); nobody in THIS kernel reads it
+    using T16 = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
+    pack_adapters_body<T16>(p.A32, p.B32, static_cast<T16*>(p.a16), static_cast<T16*>(p.a16t), static_cast<T16*>(p.sb16),
+                            static_cast<T16*>(p.sb16t), p.C, p.N, p.r, kRPad, p.s,
+                            blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x,
+                            static_cast<long long>(gridDim.x) * blockDim.x);
+  }
 
   if (warp == RP_CONSUMERS) {
     if (lane == 0) {
@@ -187,9 +214,9 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
       for (int kb = 0; kb < nk; ++kb) {
         mbar_wait(&empty[stage], phase ^ 1, 11);
         uint8_t* act = smem + stage * SLOT;
-        mbar_arrive_expect_tx(&full[stage], RP_BM * 128 + kRPad * 128);
+        mbar_arrive_expect_tx(&full[stage], RP_BM * 128 + (kDirectA ? 0 : kRPad * 128));
         tma_load_2d(act, &tmAct, &full[stage], kb * RP_BK, m0);
-        tma_load_2d(act + RP_ACT_BYTES, &tmP, &full[stage], kb * RP_BK, 0);
+        if constexpr (!kDirectA) tma_load_2d(act + RP_ACT_BYTES, &tmP, &full[stage], kb * RP_BK, 0);
         if (++stage == RP_STAGES) {
           stage = 0;
           phase ^= 1;
@@ -238,7 +265,42 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
   // Two tiles per trip: their four Philox draws are independent dependency chains (10 rounds of a wide multiply
   // feeding a 3-input XOR each), issued back to back so that they hide one another's latency; with ~4 warps per
   // scheduler a single chain per warp leaves the issue slots idle (ncu: "wait" and "math pipe throttle" stalls).
+  constexpr int NBE_MAX = kDirectA ? kNBE : NB;  // kNBE = 1: r <= 8 (the reference), half the fragment registers
+  const int nbe = kDirectA ? min((p.r + 7) >> 3, kNBE) : NB;  // n-blocks (8 rank columns each) that are not all padding
+  // kDirectA: B fragments straight from the fp32 master, fetched one trip ahead (the loads of trip t+1 are issued
+  // after trip t's MMAs and packed to 16 bits at the top of trip t+1, so their latency hides under the Philox draws
+  // and only eight registers stay live across them): lane (g8, q) holds A[n*8 + g8][c .. c+1] and [c+8 .. c+9],
+  // c = 16-column step + 2q.
+  float2 braw[2][2][NBE_MAX][2];
+  auto load_braw = [&](int kb_first) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u)
+#pragma unroll
+      for (int kk = 0; kk < 2; ++kk)
+#pragma unroll
+        for (int n = 0; n < NBE_MAX; ++n)
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int j = n * 8 + g8, c = (kb_first + u) * RP_BK + (half * 2 + kk) * 16 + h * 8 + 2 * q;
+            braw[u][kk][n][h] = (n < nbe && j < p.r && c < p.C)
+                                    ? __ldg(reinterpret_cast<const float2*>(p.A32 + static_cast<size_t>(j) * p.C + c))
+                                    : make_float2(0.f, 0.f);
+          }
+  };
+  if constexpr (kDirectA) load_braw(0);
   for (int kb0 = 0; kb0 < nk; kb0 += 2) {
+    uint32_t bpk[2][2][NBE_MAX][2];
+    if constexpr (kDirectA) {
+#pragma unroll
+      for (int u = 0; u < 2; ++u)
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk)
+#pragma unroll
+          for (int n = 0; n < NBE_MAX; ++n)
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+              bpk[u][kk][n][h] = pack2(braw[u][kk][n][h].x, braw[u][kk][n][h].y, kBf16 ? kDtypeBf16 : kDtypeFp16);
+    }
     uint32_t kmask[2][2][4];
     if (p.dropout) {
       uint32_t kw[2][2];
@@ -292,8 +354,14 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
 #pragma unroll
         for (int n = 0; n < NB; ++n) {
           uint32_t b[2];
-          const int prow = n * 8 + b_row;
-          ldsm_x2(pt_u + prow * 128 + (((ks * 2 + b_hi) ^ (prow & 7)) << 4), b);
+          if constexpr (kDirectA) {
+            if (n >= nbe || n >= NBE_MAX) continue;  // warp-uniform: all-padding rank columns contribute nothing
+            b[0] = bpk[u][kk][n < NBE_MAX ? n : 0][0];
+            b[1] = bpk[u][kk][n < NBE_MAX ? n : 0][1];
+          } else {
+            const int prow = n * 8 + b_row;
+            ldsm_x2(pt_u + prow * 128 + (((ks * 2 + b_hi) ^ (prow & 7)) << 4), b);
+          }
           mma_16816<kBf16>(acc[n], a, b);
         }
       }
@@ -304,6 +372,7 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
         phase ^= 1;
       }
     }
+    if constexpr (kDirectA) load_braw(kb0 + 2);  // columns beyond C come back as zeros
   }
 
   // acc fragment: (row = lane/4 [+8], col = n*8 + (lane%4)*2 [+1]); half 1 hands its partial
