@@ -62,7 +62,10 @@ constexpr int BIAS_BYTES = BN * 4;  // the tile's bias slice as fp32 (unmasked k
 constexpr int SMEM_BYTES = 4 * (A_TILE_BYTES + BN * BK * 2) + EPI_BYTES + BAR_BYTES + BIAS_BYTES + 1024;  // same for both
 constexpr int THREADS = 256;
 constexpr int TMEM_COLS = 512;
-constexpr int GROUP_M = 16;  // m-blocks (of one CTA or one pair) per raster group (L2 reuse of B panels)
+#ifndef LB_EXP_GROUP_M
+#define LB_EXP_GROUP_M 16
+#endif
+constexpr int GROUP_M = LB_EXP_GROUP_M;  // m-blocks (of one CTA or one pair) per raster group (L2 reuse of B panels)
 
 struct Params {
   int M, N, K1;
