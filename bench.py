@@ -45,6 +45,9 @@ def parse():
     ap.add_argument("--cpu-tokens", type=int, default=0,
                     help="tokens per step of the CPU legs (0: the reference arm uses --tokens, the cpu_baseline leg of "
                          "the product arm a 4096-token sample)")
+    ap.add_argument("--cfg1-ddp", action="store_true",
+                    help="with --impl reference under torchrun --nproc-per-node 2: BASELINE configs[0] as a real two-rank "
+                         "gloo DDP job on the host cores (every rank works)")
     ap.add_argument("--no-finetune", action="store_true",
                     help="layer workload: skip the short whole-model fine-tune runs that fill the `finetune` key")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -928,6 +931,70 @@ def run_pipeline(a, pkg, rank, world, device):
     return line
 
 
+def run_reference_cfg1(a):
+    """--impl reference --workload distilgpt2 --cfg1-ddp under `torchrun --nproc-per-node 2`: BASELINE.json
+    configs[0] / BASELINE.md section 2 "B-cfg1" exactly -- distilgpt2 architecture (random init), LoRA r=8 alpha=16
+    dropout 0.05 on c_attn / c_proj (18 modules, 405 504 trainable parameters), fp32, DDP over gloo with world_size 2,
+    seq 128, batch 4 per rank, AdamW lr 5e-5, clip 1.0 (finetune_lora_distilgpt2.py:98-104, 130-145) on the oracle's
+    layer.  3 warm-up + 20 timed optimiser steps, then the 50-step loss curve.  EVERY rank works here (the run is the
+    two-rank DDP job itself); rank 0 prints the line."""
+    import torch.distributed as dist
+    from transformers import GPT2Config, GPT2LMHeadModel
+
+    import __graft_entry__ as g
+    from oracle import lora_ref
+
+    pkg = g.load_package()
+    rank, world, _ = pkg.train.init_distributed("gloo")
+    threads = int(os.environ.get("OMP_NUM_THREADS", "0")) or max(1, len(os.sched_getaffinity(0)) // max(world, 1))
+    torch.set_num_threads(threads)
+    B, S, warm, timed, curve = 4, 128, 3, 20, 50
+    torch.manual_seed(0)  # finetune_lora_distilgpt2.py:30
+    model = GPT2LMHeadModel(GPT2Config(n_layer=6, n_embd=768, n_head=12, n_positions=1024, vocab_size=50257))
+    model.config.use_cache = False
+    pm = lora_ref.ref_get_peft_model(model, lora_ref.RefLoraConfig(r=8, lora_alpha=16, lora_dropout=0.05,
+                                                                  target_modules=["c_attn", "c_proj"]))
+    n_train = sum(p.numel() for p in pm.parameters() if p.requires_grad)
+    net = pkg.train.wrap_ddp(pm) if world > 1 else pm
+    batches = pkg.train.synthetic_batches(warm + timed + curve, B, S, 50257, 50256, seed=1234 + rank)
+    tr = pkg.train.Trainer(net, pkg.train.TrainConfig(lr=5e-5, accum=1, total_steps=warm + timed + curve))
+    tr._ensure_sched(warm + timed + curve)
+    net.train()
+
+    def step(b):
+        loss = tr.micro_step(b, sync=True)
+        tr.optimizer_step()
+        return float(loss)
+
+    for b in batches[:warm]:
+        step(b)
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for b in batches[warm:warm + timed]:
+        step(b)
+    if world > 1:
+        dist.barrier()
+    wall = time.perf_counter() - t0
+    losses = [step(b) for b in batches[warm + timed:]]
+    if rank == 0:
+        v = world * B * S * timed / wall
+        sample = f"{timed} timed optimiser steps after {warm} warm-up, {threads} threads per rank"
+        print(json.dumps({
+            "impl": "reference", "metric": "lora_finetune_tokens_per_sec", "value": v, "unit": UNIT, "n_gpus": 0,
+            "ms_per_step": wall / timed * 1e3, "steps": timed, "warmup": warm, "dtype": "f32", "data": "synthetic",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "config": {"workload": "BASELINE.json configs[0]: distilgpt2 architecture LoRA (r=8, c_attn/c_proj) DDP on "
+                                   f"CPU/gloo world_size={world}, seq {S}, batch {B} per rank, fp32, AdamW lr 5e-5, clip 1.0",
+                       "trainable_params": n_train, "parallelism": f"dp{world} (gloo)"},
+            "cpu_baseline": {"value": v, "unit": UNIT, "kind": "port", "cores": threads * world, "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0,
+            "loss_curve_50_steps": [round(x, 5) for x in losses],
+        }), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def run_reference_model(a, rank):
     """CPU arm for the model workloads: BASELINE.json configs[0] -- distilgpt2-architecture LoRA (r=8, c_attn/c_proj)
     fp32 on the host cores, synthetic tokens seq 128 batch 4 (the reference's own CPU-runnable case); for opt27b a
@@ -973,6 +1040,9 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if a.impl == "reference":
+        if a.cfg1_ddp:
+            run_reference_cfg1(a)
+            return
         if a.workload == "layer":
             run_reference(a, rank)
         else:
