@@ -88,6 +88,10 @@ FWD_BWD_CASES = [
     (130, 776, 520, 8, 0.05, True, torch.bfloat16, True),  # its Conv1D twin
     (257, 520, 776, 16, 0.05, False, torch.float16, False),  # fp16, r = 16, M one past a 256-row pair tile
     (200, 2560, 2560, 24, 0.05, False, torch.bfloat16, True),  # r -> r_pad 32 masked epilogue (smem slice flavour)
+    # rank 64 / 32 over many row tiles and several row splits of the column projections (eight-warp wide form:
+    # inline TMA producer over more tiles than ring slots, accumulators folded through the ring)
+    (2400, 2560, 2560, 64, 0.05, False, torch.bfloat16, True),
+    (1300, 768, 2304, 32, 0.05, True, torch.float16, True),
 ]
 
 

@@ -305,13 +305,13 @@ __host__ __device__ __forceinline__ uint32_t dropout_keep_byte(uint32_t m, uint3
   }
   return bits;
 }
-#ifdef __CUDACC__
 // Round keys of Philox4x32-10 for a fixed seed: hoisted out of the per-call rounds (the seed is a
-// kernel constant), which removes 20 adds from every draw.
+// kernel constant), which removes 20 adds from every draw.  The host fills them into the kernel's
+// parameter block, so the rounds can take them as constant-bank operands and no register holds a key.
 struct PhiloxKeys {
   uint32_t k[10][2];
 };
-__device__ __forceinline__ PhiloxKeys philox_round_keys(uint64_t seed) {
+__host__ __device__ __forceinline__ PhiloxKeys philox_round_keys(uint64_t seed) {
   PhiloxKeys rk;
   uint32_t k0 = static_cast<uint32_t>(seed), k1 = static_cast<uint32_t>(seed >> 32);
 #pragma unroll
@@ -323,6 +323,7 @@ __device__ __forceinline__ PhiloxKeys philox_round_keys(uint64_t seed) {
   }
   return rk;
 }
+#ifdef __CUDACC__
 // thresh14 -> the packed-half constant dropout_fragment_masks compares against
 __host__ __device__ __forceinline__ uint32_t dropout_thresh_half2(uint32_t thresh14) {
   return (thresh14 + 0x0400u) * 0x00010001u;

@@ -16,6 +16,7 @@
 
 #include "act.cuh"
 #include "ce.cuh"
+#include "colproj_sm100.cuh"
 #include "p2p.cuh"
 #include "gemm_sm100.cuh"
 #include "gemm_masked_sm100.cuh"
@@ -193,6 +194,8 @@ int device_setup(int* sm_count) {
 #define OPT_IN_SKINNY(BF, RP)                                                                     \
   CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP>, skinny::rp_smem_bytes<RP>()));             \
   CUDA_TRY(opt_in_smem(skinny::colproj_kernel<BF, RP>, skinny::cp_smem_bytes<RP>()));
+    CUDA_TRY(opt_in_smem(skinny::colproj_umma_kernel<32>, skinny::cu_smem_bytes<32>()));
+    CUDA_TRY(opt_in_smem(skinny::colproj_umma_kernel<64>, skinny::cu_smem_bytes<64>()));
     CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<true, 16, true, 1>, skinny::rp_smem_bytes<16>()));
     CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<false, 16, true, 1>, skinny::rp_smem_bytes<16>()));
     CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<true, 16, true, 2>, skinny::rp_smem_bytes<16>()));
@@ -217,13 +220,25 @@ struct Split {
 // Row splits of the column projections; sized for 148 SMs on purpose so that
 // the workspace size does not depend on the device queried.
 // `launch_tiles` = column tiles of ALL problems that share the launch (dB and dA go together).
+// Padded rank 32 / 64: the column projections run on tensor memory (colproj_sm100.cuh).  LORA_B200_COLPROJ=hmma
+// selects the warp-MMA kernel instead (A/B timing only; both are exact implementations of the same sums).
+bool colproj_on_tmem(int rp) {
+  static const bool hmma = [] {
+    const char* e = getenv("LORA_B200_COLPROJ");
+    return e && strcmp(e, "hmma") == 0;
+  }();
+  return rp >= 32 && !hmma;
+}
 Split colproj_split(int64_t M, int64_t launch_tiles, int rp) {
   const int64_t m_tiles = (M + skinny::CP_BM - 1) / skinny::CP_BM;
   // aim for at most one full wave so that no straggler wave forms: two CTAs fit per SM at padded rank 16, one at
   // 32 / 64 (128 / 168 registers); fewer, longer CTAs also amortise the per-CTA reduction and fold, which at r = 64
   // outweighed the streaming (768 -> 768: 110 us with 12 row splits)
   int64_t want = (2 * 148) / launch_tiles;
-  if (rp > 16) {  // one CTA per SM: the split count (<= 8) with the fewest CTA-waves per unit of work, ties to the smaller
+  if (colproj_on_tmem(rp)) {
+    // one CTA per SM and HBM-bound from ~100 CTAs on (192 KiB of loads in flight each): one wave, never two
+    want = 148 / launch_tiles;
+  } else if (rp > 16) {  // one CTA per SM: the split count (<= 8) with the fewest CTA-waves per unit of work, ties to the smaller
     double best = 1e30;
     for (int64_t sct = 1; sct <= 8; ++sct) {
       const double cost = static_cast<double>((launch_tiles * sct + 147) / 148) / static_cast<double>(sct);
@@ -241,7 +256,46 @@ Split colproj_split(int64_t M, int64_t launch_tiles, int rp) {
   s.splits = static_cast<int>((M + s.rows_per_split - 1) / s.rows_per_split);
   return s;
 }
-int64_t colproj_tiles(int64_t C, int rp) { return (C + skinny::cp_cols(rp) - 1) / skinny::cp_cols(rp); }
+int64_t colproj_tiles(int64_t C, int rp) {
+  const int cols = colproj_on_tmem(rp) ? skinny::CU_COLS : skinny::cp_cols(rp);
+  return (C + cols - 1) / cols;
+}
+// Row splits of each problem of one launch.  The warp-MMA kernel gives every problem the same split.  The tensor-
+// memory kernel runs one CTA per SM, so the problems' split counts are chosen together: the pair that fits one wave
+// (sum of tiles x splits <= 148) and has the shortest longest CTA, a tile of a dropout-masked problem counting
+// kMaskedTileCost tiles of a plain one (measured); ties go to the fewer CTAs.
+constexpr double kMaskedTileCost = 1.25;
+void colproj_plan(int64_t M, int njobs, const int64_t* tiles, const bool* masked, int rp, Split* out) {
+  int64_t launch_tiles = 0;
+  for (int i = 0; i < njobs; ++i) launch_tiles += tiles[i];
+  const Split same = colproj_split(M, launch_tiles, rp);
+  for (int i = 0; i < njobs; ++i) out[i] = same;
+  if (!colproj_on_tmem(rp) || njobs != 2 || launch_tiles > 148) return;
+  const int64_t m_tiles = (M + skinny::CP_BM - 1) / skinny::CP_BM;
+  const int64_t smax = std::min<int64_t>(m_tiles, 32);
+  double best = 1e30;
+  int64_t best_ctas = 0, s0 = 1, s1 = 1;
+  for (int64_t a = 1; a <= smax; ++a)
+    for (int64_t b = 1; b <= smax; ++b) {
+      const int64_t ctas = tiles[0] * a + tiles[1] * b;
+      if (ctas > 148) break;
+      const double ca = static_cast<double>((m_tiles + a - 1) / a) * (masked[0] ? kMaskedTileCost : 1.0);
+      const double cb = static_cast<double>((m_tiles + b - 1) / b) * (masked[1] ? kMaskedTileCost : 1.0);
+      const double cost = std::max(ca, cb);
+      if (cost < best - 1e-9 || (cost < best + 1e-9 && ctas < best_ctas)) {
+        best = cost;
+        best_ctas = ctas;
+        s0 = a;
+        s1 = b;
+      }
+    }
+  const int64_t want[2] = {s0, s1};
+  for (int i = 0; i < 2; ++i) {
+    const int64_t tiles_per = (m_tiles + want[i] - 1) / want[i];
+    out[i].rows_per_split = static_cast<int>(tiles_per * skinny::CP_BM);
+    out[i].splits = static_cast<int>((M + out[i].rows_per_split - 1) / out[i].rows_per_split);
+  }
+}
 
 constexpr int kMaxColTiles = 4096;  // arrival counters per column projection (C <= 4096*64 columns)
 // Packed adapter operands (written by the forward or by lora_linear_pack, read by the backward):
@@ -270,8 +324,15 @@ Workspace carve(int64_t M, int64_t K, int64_t N, int r) {
   size_t off = 0;
   w.dh = off;    off += align256(static_cast<size_t>(M) * rp * 2);
   w.counters = off; off += align256(2 * kMaxColTiles * sizeof(unsigned int));
-  const Split sp = colproj_split(M, colproj_tiles(K, rp) + colproj_tiles(N, rp), rp);
-  const size_t pk = static_cast<size_t>(sp.splits) * K * rp * 4, pn = static_cast<size_t>(sp.splits) * N * rp * 4;
+  // the backward's launch: problem 0 = dB over N columns, problem 1 = dA over K columns (masked when p > 0);
+  // sized for the larger split count of the two cases so that the size does not depend on p
+  const int64_t tiles[2] = {colproj_tiles(N, rp), colproj_tiles(K, rp)};
+  const bool with_mask[2] = {false, true}, without[2] = {false, false};
+  Split pa[2], pb[2];
+  colproj_plan(M, 2, tiles, with_mask, rp, pa);
+  colproj_plan(M, 2, tiles, without, rp, pb);
+  const size_t pn = static_cast<size_t>(std::max(pa[0].splits, pb[0].splits)) * N * rp * 4;
+  const size_t pk = static_cast<size_t>(std::max(pa[1].splits, pb[1].splits)) * K * rp * 4;
   w.partial = off;  off += align256(pn);   // dB partial sums
   w.partial2 = off; off += align256(pk);   // dA partial sums (both column projections share one launch)
   w.total = off;
@@ -343,6 +404,7 @@ int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out,
   rp_p.out_scale = out_scale;
   rp_p.dropout = p > 0.f ? 1 : 0;
   rp_p.seed = seed;
+  rp_p.rk = philox_round_keys(seed);
   rp_p.offset = offset;
   rp_p.offset_dev = reinterpret_cast<const unsigned long long*>(offset_dev);
   rp_p.thresh14 = static_cast<uint32_t>(p * 16384.0f + 0.5f);
@@ -396,8 +458,21 @@ int launch_colproj_t(const CUtensorMap (&tmAct)[2], const CUtensorMap (&tmSmall)
     gy = std::max(gy, pp.prob[i].splits);
   }
   dim3 grid(gx, gy, njobs);
-  CUDA_TRY(launch_pdl(skinny::colproj_kernel<BF, RP>, grid, dim3(skinny::CP_THREADS), skinny::cp_smem_bytes<RP>(), stream, 1,
+  CUDA_TRY(launch_pdl(skinny::colproj_kernel<BF, RP>, grid, dim3(skinny::cp_threads(RP)), skinny::cp_smem_bytes<RP>(), stream, 1,
                       tmAct[0], tmSmall[0], tmAct[1], tmSmall[1], pp));
+  return 0;
+}
+
+template <int RP>
+int launch_colproj_umma_t(const CUtensorMap (&tmAct)[2], const CUtensorMap (&tmSmall)[2], const skinny::ColProjParams& pp,
+                          int njobs, int dtype, cudaStream_t stream) {
+  int gx = 0, gy = 0;
+  for (int i = 0; i < njobs; ++i) {
+    gx = std::max(gx, pp.prob[i].c_tiles);
+    gy = std::max(gy, pp.prob[i].splits);
+  }
+  CUDA_TRY(launch_pdl(skinny::colproj_umma_kernel<RP>, dim3(gx, gy, njobs), dim3(skinny::CU_THREADS),
+                      skinny::cu_smem_bytes<RP>(), stream, 1, tmAct[0], tmSmall[0], tmAct[1], tmSmall[1], pp, dtype));
   return 0;
 }
 
@@ -407,11 +482,17 @@ int launch_colproj(const ColProjJob* jobs, int njobs, int64_t M, int r, int rp, 
                    cudaStream_t stream) {
   CUtensorMap tmAct[2], tmSmall[2];
   skinny::ColProjParams pp{};
-  int64_t launch_tiles = 0;
-  for (int i = 0; i < njobs; ++i) launch_tiles += colproj_tiles(jobs[i].C, rp);
-  const Split sp = colproj_split(M, launch_tiles, rp);
+  int64_t tiles[2] = {0, 0};
+  bool masked[2] = {false, false};
+  for (int i = 0; i < njobs; ++i) {
+    tiles[i] = colproj_tiles(jobs[i].C, rp);
+    masked[i] = jobs[i].keep != nullptr;
+  }
+  Split plan[2];
+  colproj_plan(M, njobs, tiles, masked, rp, plan);
   for (int i = 0; i < 2; ++i) {
     const ColProjJob& j = jobs[i < njobs ? i : 0];
+    const Split& sp = plan[i < njobs ? i : 0];
     if (make_tmap(&tmAct[i], j.act, dtype, j.C, M, j.C, 64, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_128B, "colproj act")) return 1;
     const CUtensorMapSwizzle ssw = rp == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : (rp == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE);
     if (make_tmap(&tmSmall[i], j.small, dtype, rp, M, rp, rp, skinny::CP_BM, ssw, "colproj small")) return 1;
@@ -432,6 +513,9 @@ int launch_colproj(const ColProjJob* jobs, int njobs, int64_t M, int r, int rp, 
     q.c_tiles = static_cast<int>(colproj_tiles(j.C, rp));
     if (q.c_tiles > kMaxColTiles) return fail("column projection over %lld columns exceeds the %d-tile counter table", (long long)j.C, kMaxColTiles);
   }
+  if (colproj_on_tmem(rp))
+    return rp == 32 ? launch_colproj_umma_t<32>(tmAct, tmSmall, pp, njobs, dtype, stream)
+                    : launch_colproj_umma_t<64>(tmAct, tmSmall, pp, njobs, dtype, stream);
   const bool bf = dtype == kDtypeBf16;
 #define CP_CASE(BF, RP) return launch_colproj_t<BF, RP>(tmAct, tmSmall, pp, njobs, stream);
   if (bf) {

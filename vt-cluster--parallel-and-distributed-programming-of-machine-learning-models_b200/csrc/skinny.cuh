@@ -150,6 +150,7 @@ struct RowProjParams {
   float out_scale;
   int dropout;  // 0/1
   uint64_t seed, offset;
+  PhiloxKeys rk;  // philox_round_keys(seed), filled by the host
   const unsigned long long* offset_dev;  // optional: *offset_dev is added to `offset` (graph-replayable RNG state)
   uint32_t thresh14;  // round(p * 16384)
   unsigned int* zero_words;  // optional: words CTA 0 clears (the column projections' arrival counters)
@@ -238,14 +239,13 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
 
   // Per-lane constants of the dropout draw.
   const int keep_ld = p.C >> 3;
-  PhiloxKeys rk;
+  const PhiloxKeys& rk = p.rk;
   const uint32_t thresh2 = dropout_thresh_half2(p.thresh14);
   const uint64_t offset = p.offset + ((p.dropout && p.offset_dev != nullptr) ? *p.offset_dev : 0ull);
   const uint32_t off_lo = static_cast<uint32_t>(offset), off_hi = static_cast<uint32_t>(offset >> 32);
   const uint32_t blocks_per_row = static_cast<uint32_t>((p.C + 15) >> 4);
   uint64_t gbase = 0;
   if (p.dropout) {
-    rk = philox_round_keys(p.seed);
     gbase = dropout_counter(static_cast<uint32_t>((m0 >> 4) + slab), static_cast<uint32_t>(half * 2), blocks_per_row,
                             static_cast<uint32_t>(lane));
   }
@@ -412,11 +412,19 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
 // one 128-byte-swizzled TMA load): kCB = 2 makes every row a 256-byte DRAM segment.  Warp 8 is
 // the TMA producer; consumer warp w owns rows 16w..16w+15 of every tile and all its columns;
 // partial sums of the 8 warps meet in shared memory; the last CTA of a column tile folds the row splits.
+// Padded rank 32 / 64 ("wide"): 64 / 128 accumulator registers per thread.  ptxas sizes the register file for
+// the thread count rounded up to four warps, so nine warps leave 168 registers and the rank-64 accumulators
+// spilled (2.3 M local loads per launch, measured); the wide form therefore runs EIGHT warps -- lane 0 of warp 0
+// also issues the TMA loads, one tile behind its own consumption -- and has 255 registers.  Its eight partial
+// accumulators meet in the tile ring (idle by then) and all threads add them at once, in warp order, instead of
+// eight serial turns of read-modify-write (which cost as much as the main loop at 19 tiles per CTA).
 // ---------------------------------------------------------------------------
 constexpr int CP_BM = 128;
 constexpr int CP_BOX_BYTES = CP_BM * 128;  // 16 KiB: 128 rows x 64 columns
 constexpr int CP_CONSUMERS = 8;
 constexpr int CP_THREADS = (CP_CONSUMERS + 1) * 32;
+__host__ __device__ constexpr bool cp_wide(int rpad) { return rpad >= 32; }
+__host__ __device__ constexpr int cp_threads(int rpad) { return cp_wide(rpad) ? CP_CONSUMERS * 32 : CP_THREADS; }
 // 64-column boxes per tile / ring depth, by padded rank (register and smem budget)
 __host__ __device__ constexpr int cp_boxes(int rpad) { return 1; }  // 2 boxes cost the second resident CTA (smem)
 __host__ __device__ constexpr int cp_cols(int rpad) { return 64 * cp_boxes(rpad); }
@@ -432,7 +440,8 @@ constexpr int CP_KEEP_STAGES = 4;  // keep-byte ring of the dA problem: 4 tiles 
 constexpr int CP_KEEP_BYTES = CP_KEEP_STAGES * CP_BM * 8;
 template <int kRPad>
 __host__ __device__ constexpr int cp_smem_bytes() {
-  return cp_stages(kRPad) * cp_slot_bytes<kRPad>() + cp_cols(kRPad) * kRPad * 4 + CP_KEEP_BYTES + 1024 + 256;
+  return cp_stages(kRPad) * cp_slot_bytes<kRPad>() + (cp_wide(kRPad) ? 0 : cp_cols(kRPad) * kRPad * 4) + CP_KEEP_BYTES +
+         1024 + 256;
 }
 __host__ __device__ constexpr int cp_min_ctas(int rpad) { return rpad <= 16 ? 2 : 1; }
 
@@ -455,7 +464,7 @@ struct ColProjParams {
 };
 
 template <bool kBf16, int kRPad>
-__global__ void __launch_bounds__(CP_THREADS, cp_min_ctas(kRPad))
+__global__ void __launch_bounds__(cp_threads(kRPad), cp_min_ctas(kRPad))
     colproj_kernel(const __grid_constant__ CUtensorMap tmAct0, const __grid_constant__ CUtensorMap tmSmall0,
                    const __grid_constant__ CUtensorMap tmAct1, const __grid_constant__ CUtensorMap tmSmall1,
                    const ColProjParams pp) {
@@ -471,10 +480,14 @@ __global__ void __launch_bounds__(CP_THREADS, cp_min_ctas(kRPad))
   constexpr int STAGES = cp_stages(kRPad);
   constexpr int ACT_BYTES = kCB * CP_BOX_BYTES;
   constexpr int NCB = 4 * kCB;  // 16-column blocks per tile
+  constexpr bool kWide = cp_wide(kRPad);
+  constexpr int THREADS = cp_threads(kRPad);
+  constexpr int SOUT_BYTES = kWide ? 0 : COLS * kRPad * 4;
+  static_assert(!kWide || STAGES * SLOT >= CP_CONSUMERS * COLS * kRPad * 4, "the tile ring holds the eight partial accumulators");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   float* sout = reinterpret_cast<float*>(smem + STAGES * SLOT);
-  uint8_t* keep_s = smem + STAGES * SLOT + COLS * kRPad * 4;  // [CP_KEEP_STAGES][128 rows][8 bytes]
+  uint8_t* keep_s = smem + STAGES * SLOT + SOUT_BYTES;  // [CP_KEEP_STAGES][128 rows][8 bytes]
   uint64_t* full = reinterpret_cast<uint64_t*>(keep_s + CP_KEEP_BYTES);
   uint64_t* empty = full + STAGES;
 
@@ -491,30 +504,31 @@ __global__ void __launch_bounds__(CP_THREADS, cp_min_ctas(kRPad))
     }
     fence_barrier_init();
   }
-  for (int i = threadIdx.x; i < COLS * kRPad; i += CP_THREADS) sout[i] = 0.f;
+  if constexpr (!kWide)
+    for (int i = threadIdx.x; i < COLS * kRPad; i += THREADS) sout[i] = 0.f;
   pdl_launch_dependents();
   __syncthreads();
   pdl_wait();
 
-  if (warp == CP_CONSUMERS) {
-    if (lane == 0) {
-      uint32_t stage = 0, phase = 0;
-      for (int t = 0; t < nt; ++t) {
-        mbar_wait(&empty[stage], phase ^ 1, 21);
-        uint8_t* act = smem + stage * SLOT;
-        mbar_arrive_expect_tx(&full[stage], ACT_BYTES + CP_BM * SROW);
+  // tile t -> ring slot t % STAGES, once every consumer warp has released the slot's previous tile
+  auto produce = [&](int t) {
+    const int st = t % STAGES;
+    mbar_wait(&empty[st], ((t / STAGES) & 1) ^ 1, 21);
+    uint8_t* act = smem + st * SLOT;
+    mbar_arrive_expect_tx(&full[st], ACT_BYTES + CP_BM * SROW);
 #pragma unroll
-        for (int bx = 0; bx < kCB; ++bx)
-          tma_load_2d(act + bx * CP_BOX_BYTES, tmAct, &full[stage], c0 + bx * 64, m_begin + t * CP_BM);
-        tma_load_2d(act + ACT_BYTES, tmSmall, &full[stage], 0, m_begin + t * CP_BM);
-        if (++stage == STAGES) {
-          stage = 0;
-          phase ^= 1;
-        }
-      }
-    }
+    for (int bx = 0; bx < kCB; ++bx)
+      tma_load_2d(act + bx * CP_BOX_BYTES, tmAct, &full[st], c0 + bx * 64, m_begin + t * CP_BM);
+    tma_load_2d(act + ACT_BYTES, tmSmall, &full[st], 0, m_begin + t * CP_BM);
+  };
+
+  if (!kWide && warp == CP_CONSUMERS) {
+    if (lane == 0)
+      for (int t = 0; t < nt; ++t) produce(t);
     __syncwarp();
   } else {
+    if (kWide && warp == 0 && lane == 0)
+      for (int t = 0; t < min(nt, STAGES); ++t) produce(t);
     float acc[NCB][NB][4];
 #pragma unroll
     for (int cbk = 0; cbk < NCB; ++cbk)
@@ -563,6 +577,8 @@ __global__ void __launch_bounds__(CP_THREADS, cp_min_ctas(kRPad))
     uint32_t stage = 0, phase = 0;
     for (int t = 0; t < nt; ++t) {
       const int mt = m_begin + t * CP_BM;
+      // wide form: the slot of tile t - 1 is refilled here, when the other warps have (nearly) left it too
+      if (kWide && warp == 0 && lane == 0 && t >= 1 && t - 1 + STAGES < nt) produce(t - 1 + STAGES);
       // per row and 32-bit half: byte c = 0xFF iff bit g8 of chunk c's keep-byte is set
       uint32_t ksel[4][2];
       if (has_keep) {
@@ -639,6 +655,22 @@ __global__ void __launch_bounds__(CP_THREADS, cp_min_ctas(kRPad))
     // The eight warps add their partial sums in warp order (named barrier 1 between turns):
     // a fixed summation order keeps dA/dB bit-reproducible, which gradient-checkpoint
     // recompute and the DDP equality tests rely on.
+    if constexpr (kWide) {
+      // every warp has left the ring: park the eight accumulators there, [warp][c][j ^ swz(c)] (the XOR spreads
+      // the eight rows of a store over the banks), then all threads add the eight copies in warp order
+      __syncthreads();
+      float* red = reinterpret_cast<float*>(smem);
+#pragma unroll
+      for (int cbk = 0; cbk < NCB; ++cbk)
+#pragma unroll
+        for (int n = 0; n < NB; ++n)
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int c = cbk * 16 + (lane >> 2) + h * 8;
+            const int j = (n * 8 + (lane & 3) * 2) ^ ((c & 7) * (kRPad / 8));
+            *reinterpret_cast<float2*>(red + (warp * COLS + c) * kRPad + j) = make_float2(acc[cbk][n][2 * h], acc[cbk][n][2 * h + 1]);
+          }
+    } else
     for (int turn = 0; turn < CP_CONSUMERS; ++turn) {
       if (warp == turn) {
 #pragma unroll
@@ -658,7 +690,18 @@ __global__ void __launch_bounds__(CP_THREADS, cp_min_ctas(kRPad))
   __syncthreads();
   float* dst = p.partial + (static_cast<size_t>(blockIdx.y) * p.C + c0) * kRPad;
   const int ncols = min(COLS, p.C - c0);
-  for (int i = threadIdx.x; i < ncols * kRPad; i += CP_THREADS) dst[i] = sout[i];
+  if constexpr (kWide) {
+    const float* red = reinterpret_cast<const float*>(smem);
+    for (int i = threadIdx.x; i < ncols * kRPad; i += THREADS) {
+      const int c = i / kRPad, jj = i % kRPad;
+      float s = 0.f;
+#pragma unroll
+      for (int w = 0; w < CP_CONSUMERS; ++w) s += red[(w * COLS + c) * kRPad + jj];
+      dst[c * kRPad + (jj ^ ((c & 7) * (kRPad / 8)))] = s;
+    }
+  } else {
+    for (int i = threadIdx.x; i < ncols * kRPad; i += THREADS) dst[i] = sout[i];
+  }
 
   // The last CTA of this column tile to finish folds the splits, always in split order 0,1,2,...
   // (the arrival order only decides WHO adds, never the order of the additions), applies the
@@ -673,7 +716,7 @@ __global__ void __launch_bounds__(CP_THREADS, cp_min_ctas(kRPad))
   __syncthreads();
   if (s_is_last) {
     __threadfence();
-    for (int i = threadIdx.x; i < ncols * p.r; i += CP_THREADS) {
+    for (int i = threadIdx.x; i < ncols * p.r; i += THREADS) {
       const int cl = i / p.r, j = i - cl * p.r;
       const float* src = p.partial + static_cast<size_t>(c0 + cl) * kRPad + j;
       // split order 0,1,2,... as before, but four loads in flight at a time: with r = 64 and a dozen splits the
