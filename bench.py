@@ -479,7 +479,7 @@ def run_point(a, pkg, rank, world, device, with_e2e=True, with_kernels=True, wit
              (", packs the adapters" if rp == 16 else ""), bind.PHASE_ROWPROJ | bind.PHASE_PACK, fwd_call,
              "hbm", M * K * esz + keep_b + M * rp * esz),
             ("rowproj_kernel backward (dH = dY sB)", bind.PHASE_ROWPROJ, bwd_call, "hbm", M * N * esz + M * rp * esz),
-            ("colproj_kernel (dB = s dY^T H and dA = dH^T drop(X), one launch)", bind.PHASE_COLPROJ, bwd_call, "hbm",
+            ("colproj_umma_kernel (dB = s dY^T H and dA = dH^T drop(X), one launch, tensor memory)", bind.PHASE_COLPROJ, bwd_call, "hbm",
              M * N * esz + M * K * esz + keep_b + 2 * M * rp * esz),
         ]
         if rp != 16:  # padded rank 16: the forward row projection packs as a side job, there is no pack launch

@@ -27,7 +27,28 @@
 namespace lb {
 namespace skinny {
 
-constexpr int CU_COLS = 128;  // columns per CTA = UMMA M
+constexpr int CP_BM = 128;                 // rows m per tile
+constexpr int CP_BOX_BYTES = CP_BM * 128;  // 16 KiB: one TMA box of 128 rows x 64 columns
+constexpr int CU_COLS = 128;               // columns per CTA = UMMA M
+
+struct ColProjProblem {
+  float* partial;          // [splits][C][kRPad] split partial sums (scratch)
+  unsigned int* counters;  // [c_tiles], zero on entry; self-resetting (atomicInc wraps)
+  const uint8_t* keep;     // [M, C/8] or null
+  float* out;              // out[c*ld_c + j*ld_j], j < r
+  long long ld_c, ld_j;
+  float scale;
+  int accumulate;
+  int r;
+  int M, C;
+  int rows_per_split;  // multiple of CP_BM
+  int splits, c_tiles;
+};
+// One launch carries up to two independent problems (dB and dA of one backward): blockIdx.z.
+struct ColProjParams {
+  ColProjProblem prob[2];
+};
+
 constexpr int CU_STAGES = 4;
 constexpr int CU_THREADS = 320;
 constexpr int CU_MASK_WARP0 = 2, CU_MASK_WARPS = 8, CU_EPI_WARPS = 4;
@@ -62,7 +83,8 @@ __global__ void __launch_bounds__(CU_THREADS, 1)
     colproj_umma_kernel(const __grid_constant__ CUtensorMap tmAct0, const __grid_constant__ CUtensorMap tmSmall0,
                         const __grid_constant__ CUtensorMap tmAct1, const __grid_constant__ CUtensorMap tmSmall1,
                         const ColProjParams pp, const int dtype) {
-  static_assert(kRPad == 32 || kRPad == 64, "TMEM columns are allocated in powers of two >= 32");
+  static_assert(kRPad == 16 || kRPad == 32 || kRPad == 64, "padded ranks of the library");
+  constexpr int TCOLS = kRPad < 32 ? 32 : kRPad;  // TMEM columns are allocated in powers of two >= 32
   const ColProjProblem& p = pp.prob[blockIdx.z];
   if (static_cast<int>(blockIdx.x) >= p.c_tiles || static_cast<int>(blockIdx.y) >= p.splits) return;  // CTA-uniform
   const CUtensorMap* tmAct = blockIdx.z == 0 ? &tmAct0 : &tmAct1;
@@ -95,7 +117,7 @@ __global__ void __launch_bounds__(CU_THREADS, 1)
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, kRPad);
+    tmem_alloc(tmem_slot, TCOLS);
     tmem_relinquish();
   }
   pdl_launch_dependents();
@@ -125,7 +147,7 @@ __global__ void __launch_bounds__(CU_THREADS, 1)
     if (lane == 0) {
       const uint32_t idesc = make_idesc_f16(dtype == kDtypeBf16 ? 1 : 0, CU_COLS, kRPad, 1, 1);
       const uint32_t ring_u = smem_u32(smem);
-      const uint32_t small_layout = SROW == 128 ? 2u : 4u;
+      const uint32_t small_layout = SROW == 128 ? 2u : (SROW == 64 ? 4u : 6u);
       for (int t = 0; t < nt; ++t) {
         const int st = t % CU_STAGES;
         mbar_wait(has_keep ? &masked[st] : &full[st], (t / CU_STAGES) & 1, 32);
@@ -229,7 +251,7 @@ __global__ void __launch_bounds__(CU_THREADS, 1)
         if (!live) continue;
         if (p.splits == 1) {  // nothing to fold: scale and write the gradient (0 + v: what the fold computes)
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
+          for (int i = 0; i < (kRPad < 32 ? kRPad : 32); ++i)
             if (j0 + i < p.r) {
               float* e = o + static_cast<long long>(j0 + i) * p.ld_j;
               const float val = p.scale * (0.f + __uint_as_float(v[i]));
@@ -237,7 +259,7 @@ __global__ void __launch_bounds__(CU_THREADS, 1)
             }
         } else {
 #pragma unroll
-          for (int i = 0; i < 32; i += 4)
+          for (int i = 0; i < (kRPad < 32 ? kRPad : 32); i += 4)
             *reinterpret_cast<uint4*>(dst + j0 + i) = make_uint4(v[i], v[i + 1], v[i + 2], v[i + 3]);
         }
       }
@@ -250,7 +272,7 @@ __global__ void __launch_bounds__(CU_THREADS, 1)
   tc_fence_before();
   __threadfence();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, kRPad);
+  if (warp == 1) tmem_dealloc(tmem_base, TCOLS);
   if (p.splits == 1) return;  // CTA-uniform
   if (threadIdx.x == 0) {
     const unsigned int prev = atomicInc(p.counters + blockIdx.x, static_cast<unsigned int>(p.splits - 1));

@@ -31,25 +31,6 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
-// Explicit shared-space 8-byte accesses and the 8-byte asynchronous global -> shared copy (cp.async, LDGSTS)
-// used for the small keep-byte side stream of the column projection.
-__device__ __forceinline__ uint2 lds64(uint32_t saddr) {
-  uint2 v;
-  asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(saddr));
-  return v;
-}
-__device__ __forceinline__ void sts64(uint32_t saddr, const uint2 v) {
-  asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(saddr), "r"(v.x), "r"(v.y) : "memory");
-}
-__device__ __forceinline__ void cp_async8(uint32_t saddr, const void* gptr) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(saddr), "l"(gptr) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-
 // ---------------------------------------------------------------------------
 // Programmatic dependent launch: every kernel of a forward/backward call is launched with the
 // programmatic-stream-serialization attribute, signals `launch_dependents` at once (the next

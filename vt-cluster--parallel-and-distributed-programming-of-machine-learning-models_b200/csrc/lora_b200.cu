@@ -191,9 +191,8 @@ int device_setup(int* sm_count) {
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false, false, true>, gemm::SMEM_BYTES));
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false, true, true>, gemm::SMEM_BYTES));
     CUDA_TRY(opt_in_smem(gemm::gemm_masked_kernel, gemm::SMEM_BYTES));
-#define OPT_IN_SKINNY(BF, RP)                                                                     \
-  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP>, skinny::rp_smem_bytes<RP>()));             \
-  CUDA_TRY(opt_in_smem(skinny::colproj_kernel<BF, RP>, skinny::cp_smem_bytes<RP>()));
+#define OPT_IN_SKINNY(BF, RP) CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP>, skinny::rp_smem_bytes<RP>()));
+    CUDA_TRY(opt_in_smem(skinny::colproj_umma_kernel<16>, skinny::cu_smem_bytes<16>()));
     CUDA_TRY(opt_in_smem(skinny::colproj_umma_kernel<32>, skinny::cu_smem_bytes<32>()));
     CUDA_TRY(opt_in_smem(skinny::colproj_umma_kernel<64>, skinny::cu_smem_bytes<64>()));
     CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<true, 16, true, 1>, skinny::rp_smem_bytes<16>()));
@@ -217,80 +216,40 @@ struct Split {
   int splits;
   int rows_per_split;
 };
-// Row splits of the column projections; sized for 148 SMs on purpose so that
-// the workspace size does not depend on the device queried.
-// `launch_tiles` = column tiles of ALL problems that share the launch (dB and dA go together).
-// Padded rank 32 / 64: the column projections run on tensor memory (colproj_sm100.cuh).  LORA_B200_COLPROJ=hmma
-// selects the warp-MMA kernel instead (A/B timing only; both are exact implementations of the same sums).
-bool colproj_on_tmem(int rp) {
-  static const bool hmma = [] {
-    const char* e = getenv("LORA_B200_COLPROJ");
-    return e && strcmp(e, "hmma") == 0;
-  }();
-  return rp >= 32 && !hmma;
-}
-Split colproj_split(int64_t M, int64_t launch_tiles, int rp) {
-  const int64_t m_tiles = (M + skinny::CP_BM - 1) / skinny::CP_BM;
-  // aim for at most one full wave so that no straggler wave forms: two CTAs fit per SM at padded rank 16, one at
-  // 32 / 64 (128 / 168 registers); fewer, longer CTAs also amortise the per-CTA reduction and fold, which at r = 64
-  // outweighed the streaming (768 -> 768: 110 us with 12 row splits)
-  int64_t want = (2 * 148) / launch_tiles;
-  if (colproj_on_tmem(rp)) {
-    // one CTA per SM and HBM-bound from ~100 CTAs on (192 KiB of loads in flight each): one wave, never two
-    want = 148 / launch_tiles;
-  } else if (rp > 16) {  // one CTA per SM: the split count (<= 8) with the fewest CTA-waves per unit of work, ties to the smaller
-    double best = 1e30;
-    for (int64_t sct = 1; sct <= 8; ++sct) {
-      const double cost = static_cast<double>((launch_tiles * sct + 147) / 148) / static_cast<double>(sct);
-      if (cost < best - 1e-9) {
-        best = cost;
-        want = sct;
-      }
-    }
-  }
-  if (want < 1) want = 1;
-  if (want > m_tiles) want = m_tiles;
-  const int64_t tiles_per = (m_tiles + want - 1) / want;
-  Split s;
-  s.rows_per_split = static_cast<int>(tiles_per * skinny::CP_BM);
-  s.splits = static_cast<int>((M + s.rows_per_split - 1) / s.rows_per_split);
-  return s;
-}
-int64_t colproj_tiles(int64_t C, int rp) {
-  const int cols = colproj_on_tmem(rp) ? skinny::CU_COLS : skinny::cp_cols(rp);
-  return (C + cols - 1) / cols;
-}
-// Row splits of each problem of one launch.  The warp-MMA kernel gives every problem the same split.  The tensor-
-// memory kernel runs one CTA per SM, so the problems' split counts are chosen together: the pair that fits one wave
-// (sum of tiles x splits <= 148) and has the shortest longest CTA, a tile of a dropout-masked problem counting
-// kMaskedTileCost tiles of a plain one (measured); ties go to the fewer CTAs.
+// Row splits of the column projections (colproj_sm100.cuh); sized for 148 SMs on purpose so that the workspace size
+// does not depend on the device queried.  The kernel runs one CTA per SM and is HBM-bound from ~100 CTAs on (three
+// tiles of loads in flight each), so a launch is planned as ONE wave, never two: with a single problem the most
+// splits that fit; with two problems (dB and dA of one backward) the pair of split counts whose longest CTA is
+// shortest, a tile of a dropout-masked problem counting kMaskedTileCost tiles of a plain one (measured: the mask pass
+// shares the shared-memory bandwidth the tensor core reads with); ties go to the fewer CTAs.  More column tiles than
+// SMs: one split each.
 constexpr double kMaskedTileCost = 1.25;
-void colproj_plan(int64_t M, int njobs, const int64_t* tiles, const bool* masked, int rp, Split* out) {
-  int64_t launch_tiles = 0;
-  for (int i = 0; i < njobs; ++i) launch_tiles += tiles[i];
-  const Split same = colproj_split(M, launch_tiles, rp);
-  for (int i = 0; i < njobs; ++i) out[i] = same;
-  if (!colproj_on_tmem(rp) || njobs != 2 || launch_tiles > 148) return;
+int64_t colproj_tiles(int64_t C) { return (C + skinny::CU_COLS - 1) / skinny::CU_COLS; }
+void colproj_plan(int64_t M, int njobs, const int64_t* tiles, const bool* masked, Split* out) {
   const int64_t m_tiles = (M + skinny::CP_BM - 1) / skinny::CP_BM;
-  const int64_t smax = std::min<int64_t>(m_tiles, 32);
-  double best = 1e30;
-  int64_t best_ctas = 0, s0 = 1, s1 = 1;
-  for (int64_t a = 1; a <= smax; ++a)
-    for (int64_t b = 1; b <= smax; ++b) {
-      const int64_t ctas = tiles[0] * a + tiles[1] * b;
-      if (ctas > 148) break;
-      const double ca = static_cast<double>((m_tiles + a - 1) / a) * (masked[0] ? kMaskedTileCost : 1.0);
-      const double cb = static_cast<double>((m_tiles + b - 1) / b) * (masked[1] ? kMaskedTileCost : 1.0);
-      const double cost = std::max(ca, cb);
-      if (cost < best - 1e-9 || (cost < best + 1e-9 && ctas < best_ctas)) {
-        best = cost;
-        best_ctas = ctas;
-        s0 = a;
-        s1 = b;
+  int64_t want[2] = {1, 1};
+  if (njobs == 1) {
+    want[0] = std::max<int64_t>(1, std::min<int64_t>(m_tiles, 148 / tiles[0]));
+  } else if (tiles[0] + tiles[1] <= 148) {
+    const int64_t smax = std::min<int64_t>(m_tiles, 32);
+    double best = 1e30;
+    int64_t best_ctas = 0;
+    for (int64_t a = 1; a <= smax; ++a)
+      for (int64_t b = 1; b <= smax; ++b) {
+        const int64_t ctas = tiles[0] * a + tiles[1] * b;
+        if (ctas > 148) break;
+        const double ca = static_cast<double>((m_tiles + a - 1) / a) * (masked[0] ? kMaskedTileCost : 1.0);
+        const double cb = static_cast<double>((m_tiles + b - 1) / b) * (masked[1] ? kMaskedTileCost : 1.0);
+        const double cost = std::max(ca, cb);
+        if (cost < best - 1e-9 || (cost < best + 1e-9 && ctas < best_ctas)) {
+          best = cost;
+          best_ctas = ctas;
+          want[0] = a;
+          want[1] = b;
+        }
       }
-    }
-  const int64_t want[2] = {s0, s1};
-  for (int i = 0; i < 2; ++i) {
+  }
+  for (int i = 0; i < njobs; ++i) {
     const int64_t tiles_per = (m_tiles + want[i] - 1) / want[i];
     out[i].rows_per_split = static_cast<int>(tiles_per * skinny::CP_BM);
     out[i].splits = static_cast<int>((M + out[i].rows_per_split - 1) / out[i].rows_per_split);
@@ -326,11 +285,11 @@ Workspace carve(int64_t M, int64_t K, int64_t N, int r) {
   w.counters = off; off += align256(2 * kMaxColTiles * sizeof(unsigned int));
   // the backward's launch: problem 0 = dB over N columns, problem 1 = dA over K columns (masked when p > 0);
   // sized for the larger split count of the two cases so that the size does not depend on p
-  const int64_t tiles[2] = {colproj_tiles(N, rp), colproj_tiles(K, rp)};
+  const int64_t tiles[2] = {colproj_tiles(N), colproj_tiles(K)};
   const bool with_mask[2] = {false, true}, without[2] = {false, false};
   Split pa[2], pb[2];
-  colproj_plan(M, 2, tiles, with_mask, rp, pa);
-  colproj_plan(M, 2, tiles, without, rp, pb);
+  colproj_plan(M, 2, tiles, with_mask, pa);
+  colproj_plan(M, 2, tiles, without, pb);
   const size_t pn = static_cast<size_t>(std::max(pa[0].splits, pb[0].splits)) * N * rp * 4;
   const size_t pk = static_cast<size_t>(std::max(pa[1].splits, pb[1].splits)) * K * rp * 4;
   w.partial = off;  off += align256(pn);   // dB partial sums
@@ -449,20 +408,6 @@ struct ColProjJob {
   float scale;
 };
 
-template <bool BF, int RP>
-int launch_colproj_t(const CUtensorMap (&tmAct)[2], const CUtensorMap (&tmSmall)[2], const skinny::ColProjParams& pp,
-                     int njobs, cudaStream_t stream) {
-  int gx = 0, gy = 0;
-  for (int i = 0; i < njobs; ++i) {
-    gx = std::max(gx, pp.prob[i].c_tiles);
-    gy = std::max(gy, pp.prob[i].splits);
-  }
-  dim3 grid(gx, gy, njobs);
-  CUDA_TRY(launch_pdl(skinny::colproj_kernel<BF, RP>, grid, dim3(skinny::cp_threads(RP)), skinny::cp_smem_bytes<RP>(), stream, 1,
-                      tmAct[0], tmSmall[0], tmAct[1], tmSmall[1], pp));
-  return 0;
-}
-
 template <int RP>
 int launch_colproj_umma_t(const CUtensorMap (&tmAct)[2], const CUtensorMap (&tmSmall)[2], const skinny::ColProjParams& pp,
                           int njobs, int dtype, cudaStream_t stream) {
@@ -485,16 +430,17 @@ int launch_colproj(const ColProjJob* jobs, int njobs, int64_t M, int r, int rp, 
   int64_t tiles[2] = {0, 0};
   bool masked[2] = {false, false};
   for (int i = 0; i < njobs; ++i) {
-    tiles[i] = colproj_tiles(jobs[i].C, rp);
+    tiles[i] = colproj_tiles(jobs[i].C);
     masked[i] = jobs[i].keep != nullptr;
   }
   Split plan[2];
-  colproj_plan(M, njobs, tiles, masked, rp, plan);
+  colproj_plan(M, njobs, tiles, masked, plan);
   for (int i = 0; i < 2; ++i) {
     const ColProjJob& j = jobs[i < njobs ? i : 0];
     const Split& sp = plan[i < njobs ? i : 0];
     if (make_tmap(&tmAct[i], j.act, dtype, j.C, M, j.C, 64, skinny::CP_BM, CU_TENSOR_MAP_SWIZZLE_128B, "colproj act")) return 1;
-    const CUtensorMapSwizzle ssw = rp == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : (rp == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE);
+    // the Small tile's rows are r_pad elements long: swizzle span = row bytes
+    const CUtensorMapSwizzle ssw = rp == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : (rp == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
     if (make_tmap(&tmSmall[i], j.small, dtype, rp, M, rp, rp, skinny::CP_BM, ssw, "colproj small")) return 1;
     skinny::ColProjProblem& q = pp.prob[i];
     q.partial = j.partial;
@@ -510,20 +456,12 @@ int launch_colproj(const ColProjJob* jobs, int njobs, int64_t M, int r, int rp, 
     q.C = (int)j.C;
     q.rows_per_split = sp.rows_per_split;
     q.splits = sp.splits;
-    q.c_tiles = static_cast<int>(colproj_tiles(j.C, rp));
+    q.c_tiles = static_cast<int>(colproj_tiles(j.C));
     if (q.c_tiles > kMaxColTiles) return fail("column projection over %lld columns exceeds the %d-tile counter table", (long long)j.C, kMaxColTiles);
   }
-  if (colproj_on_tmem(rp))
-    return rp == 32 ? launch_colproj_umma_t<32>(tmAct, tmSmall, pp, njobs, dtype, stream)
-                    : launch_colproj_umma_t<64>(tmAct, tmSmall, pp, njobs, dtype, stream);
-  const bool bf = dtype == kDtypeBf16;
-#define CP_CASE(BF, RP) return launch_colproj_t<BF, RP>(tmAct, tmSmall, pp, njobs, stream);
-  if (bf) {
-    if (rp == 16) CP_CASE(true, 16) else if (rp == 32) CP_CASE(true, 32) else CP_CASE(true, 64)
-  } else {
-    if (rp == 16) CP_CASE(false, 16) else if (rp == 32) CP_CASE(false, 32) else CP_CASE(false, 64)
-  }
-#undef CP_CASE
+  return rp == 16 ? launch_colproj_umma_t<16>(tmAct, tmSmall, pp, njobs, dtype, stream)
+                  : (rp == 32 ? launch_colproj_umma_t<32>(tmAct, tmSmall, pp, njobs, dtype, stream)
+                              : launch_colproj_umma_t<64>(tmAct, tmSmall, pp, njobs, dtype, stream));
 }
 
 struct GemmArgs {
@@ -901,7 +839,10 @@ int lora_linear_grad_b_static(const void* dY, const void* H, float* dB, int64_t 
   if (dtype != kDtypeBf16 && dtype != kDtypeFp16) return fail("lora_linear_grad_b_static: dtype must be 0 (bf16) or 1 (fp16)");
   if (!dY || !H || !dB) return fail("lora_linear_grad_b_static: null pointer argument");
   const int rp = rpad_of(r);
-  const Split sp = colproj_split(M, colproj_tiles(N, rp), rp);
+  const int64_t tiles = colproj_tiles(N);
+  const bool no_mask = false;
+  Split sp;
+  colproj_plan(M, 1, &tiles, &no_mask, &sp);
   const size_t counter_bytes = align256(kMaxColTiles * sizeof(unsigned int));
   const size_t need = counter_bytes + static_cast<size_t>(sp.splits) * static_cast<size_t>(N) * rp * sizeof(float);
   if (need > static_cast<size_t>(LORA_B200_STATIC_SCRATCH_BYTES))

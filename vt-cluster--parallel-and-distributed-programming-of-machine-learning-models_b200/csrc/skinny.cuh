@@ -1,10 +1,10 @@
-// HBM-bound companions of the tcgen05 GEMM: everything whose arithmetic
-// intensity is ~r flop/byte: the rank-r projections
+// HBM-bound companions of the tcgen05 GEMM: the row projections, whose arithmetic
+// intensity is ~r flop/byte,
 //     H  = drop(X) A^T          dH = dY (sB)            (rowproj)
-//     dB = s dY^T H             dA = dH^T drop(X)       (colproj + reduce)
 // plus the fp32 -> 16-bit adapter packing.  They stream the activation once
 // through a TMA + mbarrier ring and use warp-level mma.sync on the tiles:
-// the tensor pipe is nowhere near the limit here, HBM is.
+// the tensor pipe is nowhere near the limit here, HBM is.  (The column
+// projections dB = s dY^T H, dA = dH^T drop(X) are in colproj_sm100.cuh.)
 //
 // Follows peft lora.Linear semantics as used at
 // finetune_lora_distilgpt2.py:98-104 / finetune_lora_opt_pp.py:104-112:
@@ -28,16 +28,6 @@ __device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
 }
 __device__ __forceinline__ void ldsm_x2(uint32_t addr, uint32_t (&r)[2]) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x2.shared.b16 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(addr));
-}
-__device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t (&r)[4]) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
-               : "r"(addr));
-}
-__device__ __forceinline__ void ldsm_x2_t(uint32_t addr, uint32_t (&r)[2]) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0,%1}, [%2];"
-               : "=r"(r[0]), "=r"(r[1])
-               : "r"(addr));
 }
 template <bool kBf16>
 __device__ __forceinline__ void mma_16816(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
@@ -401,340 +391,6 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
       if (r0 + 8 < p.M)
         out[(static_cast<size_t>(r0 + 8) * kRPad + col) >> 1] =
             pack2((acc[n][2] + o1.x) * p.out_scale, (acc[n][3] + o1.y) * p.out_scale, kBf16 ? kDtypeBf16 : kDtypeFp16);
-    }
-  }
-}
-
-// ---------------------------------------------------------------------------
-// colproj: partial[split][C, kRPad] = sum over the split's rows m of
-//          (keep .* Act)[m, c] * Small[m, j]        (fp32)
-// grid = (ceil(C / (64*kCB)), splits).  A tile is 128 rows x kCB boxes of 64 columns (each box
-// one 128-byte-swizzled TMA load): kCB = 2 makes every row a 256-byte DRAM segment.  Warp 8 is
-// the TMA producer; consumer warp w owns rows 16w..16w+15 of every tile and all its columns;
-// partial sums of the 8 warps meet in shared memory; the last CTA of a column tile folds the row splits.
-// Padded rank 32 / 64 ("wide"): 64 / 128 accumulator registers per thread.  ptxas sizes the register file for
-// the thread count rounded up to four warps, so nine warps leave 168 registers and the rank-64 accumulators
-// spilled (2.3 M local loads per launch, measured); the wide form therefore runs EIGHT warps -- lane 0 of warp 0
-// also issues the TMA loads, one tile behind its own consumption -- and has 255 registers.  Its eight partial
-// accumulators meet in the tile ring (idle by then) and all threads add them at once, in warp order, instead of
-// eight serial turns of read-modify-write (which cost as much as the main loop at 19 tiles per CTA).
-// ---------------------------------------------------------------------------
-constexpr int CP_BM = 128;
-constexpr int CP_BOX_BYTES = CP_BM * 128;  // 16 KiB: 128 rows x 64 columns
-constexpr int CP_CONSUMERS = 8;
-constexpr int CP_THREADS = (CP_CONSUMERS + 1) * 32;
-__host__ __device__ constexpr bool cp_wide(int rpad) { return rpad >= 32; }
-__host__ __device__ constexpr int cp_threads(int rpad) { return cp_wide(rpad) ? CP_CONSUMERS * 32 : CP_THREADS; }
-// 64-column boxes per tile / ring depth, by padded rank (register and smem budget)
-__host__ __device__ constexpr int cp_boxes(int rpad) { return 1; }  // 2 boxes cost the second resident CTA (smem)
-__host__ __device__ constexpr int cp_cols(int rpad) { return 64 * cp_boxes(rpad); }
-#ifndef LB_EXP_CP_STAGES
-#define LB_EXP_CP_STAGES 4
-#endif
-__host__ __device__ constexpr int cp_stages(int rpad) { return LB_EXP_CP_STAGES; }
-template <int kRPad>
-__host__ __device__ constexpr int cp_slot_bytes() {
-  return cp_boxes(kRPad) * CP_BOX_BYTES + ((CP_BM * kRPad * 2 + 1023) / 1024) * 1024;
-}
-constexpr int CP_KEEP_STAGES = 4;  // keep-byte ring of the dA problem: 4 tiles x 128 rows x 8 bytes
-constexpr int CP_KEEP_BYTES = CP_KEEP_STAGES * CP_BM * 8;
-template <int kRPad>
-__host__ __device__ constexpr int cp_smem_bytes() {
-  return cp_stages(kRPad) * cp_slot_bytes<kRPad>() + (cp_wide(kRPad) ? 0 : cp_cols(kRPad) * kRPad * 4) + CP_KEEP_BYTES +
-         1024 + 256;
-}
-__host__ __device__ constexpr int cp_min_ctas(int rpad) { return rpad <= 16 ? 2 : 1; }
-
-struct ColProjProblem {
-  float* partial;          // [splits][C][kRPad] split partial sums (scratch)
-  unsigned int* counters;  // [c_tiles], zero on entry; self-resetting (atomicInc wraps)
-  const uint8_t* keep;     // [M, C/8] or null
-  float* out;              // out[c*ld_c + j*ld_j], j < r
-  long long ld_c, ld_j;
-  float scale;
-  int accumulate;
-  int r;
-  int M, C;
-  int rows_per_split;  // multiple of CP_BM
-  int splits, c_tiles;
-};
-// One launch carries up to two independent problems (dB and dA of one backward): blockIdx.z.
-struct ColProjParams {
-  ColProjProblem prob[2];
-};
-
-template <bool kBf16, int kRPad>
-__global__ void __launch_bounds__(cp_threads(kRPad), cp_min_ctas(kRPad))
-    colproj_kernel(const __grid_constant__ CUtensorMap tmAct0, const __grid_constant__ CUtensorMap tmSmall0,
-                   const __grid_constant__ CUtensorMap tmAct1, const __grid_constant__ CUtensorMap tmSmall1,
-                   const ColProjParams pp) {
-  const ColProjProblem& p = pp.prob[blockIdx.z];
-  if (static_cast<int>(blockIdx.x) >= p.c_tiles || static_cast<int>(blockIdx.y) >= p.splits) return;  // CTA-uniform
-  const CUtensorMap* tmAct = blockIdx.z == 0 ? &tmAct0 : &tmAct1;
-  const CUtensorMap* tmSmall = blockIdx.z == 0 ? &tmSmall0 : &tmSmall1;
-  constexpr int SLOT = cp_slot_bytes<kRPad>();
-  constexpr int NB = kRPad / 8;
-  constexpr int SROW = kRPad * 2;  // bytes per row of the Small tile
-  constexpr int kCB = cp_boxes(kRPad);
-  constexpr int COLS = 64 * kCB;
-  constexpr int STAGES = cp_stages(kRPad);
-  constexpr int ACT_BYTES = kCB * CP_BOX_BYTES;
-  constexpr int NCB = 4 * kCB;  // 16-column blocks per tile
-  constexpr bool kWide = cp_wide(kRPad);
-  constexpr int THREADS = cp_threads(kRPad);
-  constexpr int SOUT_BYTES = kWide ? 0 : COLS * kRPad * 4;
-  static_assert(!kWide || STAGES * SLOT >= CP_CONSUMERS * COLS * kRPad * 4, "the tile ring holds the eight partial accumulators");
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  float* sout = reinterpret_cast<float*>(smem + STAGES * SLOT);
-  uint8_t* keep_s = smem + STAGES * SLOT + SOUT_BYTES;  // [CP_KEEP_STAGES][128 rows][8 bytes]
-  uint64_t* full = reinterpret_cast<uint64_t*>(keep_s + CP_KEEP_BYTES);
-  uint64_t* empty = full + STAGES;
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int c0 = blockIdx.x * COLS;
-  const int m_begin = blockIdx.y * p.rows_per_split;
-  const int m_end = min(p.M, m_begin + p.rows_per_split);
-  const int nt = (m_end > m_begin) ? (m_end - m_begin + CP_BM - 1) / CP_BM : 0;
-
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < STAGES; ++i) {
-      mbar_init(&full[i], 1);
-      mbar_init(&empty[i], CP_CONSUMERS);
-    }
-    fence_barrier_init();
-  }
-  if constexpr (!kWide)
-    for (int i = threadIdx.x; i < COLS * kRPad; i += THREADS) sout[i] = 0.f;
-  pdl_launch_dependents();
-  __syncthreads();
-  pdl_wait();
-
-  // tile t -> ring slot t % STAGES, once every consumer warp has released the slot's previous tile
-  auto produce = [&](int t) {
-    const int st = t % STAGES;
-    mbar_wait(&empty[st], ((t / STAGES) & 1) ^ 1, 21);
-    uint8_t* act = smem + st * SLOT;
-    mbar_arrive_expect_tx(&full[st], ACT_BYTES + CP_BM * SROW);
-#pragma unroll
-    for (int bx = 0; bx < kCB; ++bx)
-      tma_load_2d(act + bx * CP_BOX_BYTES, tmAct, &full[st], c0 + bx * 64, m_begin + t * CP_BM);
-    tma_load_2d(act + ACT_BYTES, tmSmall, &full[st], 0, m_begin + t * CP_BM);
-  };
-
-  if (!kWide && warp == CP_CONSUMERS) {
-    if (lane == 0)
-      for (int t = 0; t < nt; ++t) produce(t);
-    __syncwarp();
-  } else {
-    if (kWide && warp == 0 && lane == 0)
-      for (int t = 0; t < min(nt, STAGES); ++t) produce(t);
-    float acc[NCB][NB][4];
-#pragma unroll
-    for (int cbk = 0; cbk < NCB; ++cbk)
-#pragma unroll
-      for (int n = 0; n < NB; ++n)
-#pragma unroll
-        for (int e = 0; e < 4; ++e) acc[cbk][n][e] = 0.f;
-
-    const int keep_ld = p.C >> 3;
-    // Dropout mask of the activation (dA = dH^T drop(X)): applied to the transposed ldmatrix fragments in
-    // registers.  Register a[j] of a 16x16 block holds the two elements (rows 2q, 2q+1 [+8], one column g) of
-    // one 16-byte chunk; their keep-bits are bit g of that chunk's keep-byte in rows 2q and 2q+1.  A warp
-    // needs the 8 keep-bytes (64 columns) of each of its 16 rows per tile: lanes 0..15 copy them, 8 bytes
-    // each, into a small ring in shared memory with cp.async three tiles ahead (the loads come from HBM -- the
-    // step streams far more than L2 between the forward that wrote them and this kernel -- and no register is
-    // held while they are in flight); the ring slice of a warp is private to it, so a warp-level sync suffices.
-    static_assert(kCB == 1, "the register masking below assumes 64-column tiles");
-    constexpr int PF = CP_KEEP_STAGES - 1;
-    const int g8 = lane >> 2, q4 = lane & 3;
-    const bool has_keep = p.keep != nullptr;
-    const bool kfast = has_keep && (((keep_ld | static_cast<int>(reinterpret_cast<uintptr_t>(p.keep))) & 7) == 0) &&
-                       c0 + 64 <= p.C;
-    const uint32_t keep_u = smem_u32(keep_s) + warp * 16 * 8;
-    auto issue_keep = [&](int t) {  // keep-bytes of tile t -> ring slot t % CP_KEEP_STAGES (lanes 0..15: one row each)
-      if (t < nt && lane < 16) {
-        const int m = m_begin + t * CP_BM + warp * 16 + lane;
-        const uint32_t dst = keep_u + (t % CP_KEEP_STAGES) * (CP_BM * 8) + lane * 8;
-        const uint8_t* src = p.keep + static_cast<size_t>(m) * keep_ld + (c0 >> 3);
-        if (m < p.M && kfast) {
-          cp_async8(dst, src);
-        } else {
-          uint32_t w[2] = {0xFFFFFFFFu, 0xFFFFFFFFu};
-          if (m < p.M) {
-#pragma unroll
-            for (int c = 0; c < 8; ++c)
-              if ((c0 >> 3) + c < keep_ld)
-                w[c >> 2] = (w[c >> 2] & ~(0xFFu << (8 * (c & 3)))) | (static_cast<uint32_t>(__ldg(src + c)) << (8 * (c & 3)));
-          }
-          sts64(dst, make_uint2(w[0], w[1]));
-        }
-      }
-      cp_async_commit();  // one group per tile, also when this lane copied nothing: the counting stays uniform
-    };
-    if (has_keep)
-      for (int t = 0; t < PF; ++t) issue_keep(t);
-    uint32_t stage = 0, phase = 0;
-    for (int t = 0; t < nt; ++t) {
-      const int mt = m_begin + t * CP_BM;
-      // wide form: the slot of tile t - 1 is refilled here, when the other warps have (nearly) left it too
-      if (kWide && warp == 0 && lane == 0 && t >= 1 && t - 1 + STAGES < nt) produce(t - 1 + STAGES);
-      // per row and 32-bit half: byte c = 0xFF iff bit g8 of chunk c's keep-byte is set
-      uint32_t ksel[4][2];
-      if (has_keep) {
-        issue_keep(t + PF);
-        cp_async_wait<PF>();  // this lane's copy for tile t has landed
-        __syncwarp();         // ... and so have the other lanes' (the slice is this warp's own)
-        const uint32_t src = keep_u + (t % CP_KEEP_STAGES) * (CP_BM * 8);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const uint2 kr = lds64(src + ((j >> 1) * 8 + 2 * q4 + (j & 1)) * 8);
-          ksel[j][0] = ((kr.x >> g8) & 0x01010101u) * 0xFFu;
-          ksel[j][1] = ((kr.y >> g8) & 0x01010101u) * 0xFFu;
-        }
-      }
-      mbar_wait(&full[stage], phase, 22);
-      uint8_t* act = smem + stage * SLOT;
-      // Rows of the last tile of a split that belong to the next split (or lie
-      // beyond M, where TMA filled zeros) must not contribute.
-      const int valid_rows = m_end - mt;  // > 0
-      const uint32_t act_u = smem_u32(act), sm_u = act_u + ACT_BYTES;
-      const bool warp_live = warp * 16 < valid_rows;
-      if (warp_live) {
-        uint32_t b[NB][2];
-#pragma unroll
-        for (int n = 0; n < NB; ++n) {
-          const int mrow = warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
-          // rows of 64 / 128 bytes are stored TMA-swizzled (16-byte chunk index XOR row bits): unswizzled, the eight
-          // row addresses of an ldmatrix fall into the same banks (8-way conflict at r_pad = 64)
-          const int chunk = kRPad == 64 ? (n ^ (mrow & 7)) : (kRPad == 32 ? (n ^ ((mrow >> 1) & 3)) : n);
-          ldsm_x2_t(sm_u + mrow * SROW + chunk * 16, b[n]);
-        }
-        if (warp * 16 + 16 > valid_rows) {
-          // Partially valid 16-row slab: zero B-fragment entries of dead rows.
-          // b[n][0] holds k = (lane%4)*2 + {0,1}, b[n][1] holds k + 8.
-#pragma unroll
-          for (int n = 0; n < NB; ++n)
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              const int k = warp * 16 + h * 8 + (lane & 3) * 2;
-              uint32_t msk = 0;
-              if (k < valid_rows) msk |= 0x0000FFFFu;
-              if (k + 1 < valid_rows) msk |= 0xFFFF0000u;
-              b[n][h] &= msk;
-            }
-        }
-#pragma unroll
-        for (int cbk = 0; cbk < NCB; ++cbk) {
-          uint32_t a[4];
-          const int q = lane >> 3, i = lane & 7;
-          const int mrow = warp * 16 + (q >> 1) * 8 + i;
-          const int ch = (cbk & 3) * 2 + (q & 1);
-          ldsm_x4_t(act_u + (cbk >> 2) * CP_BOX_BYTES + mrow * 128 + ((ch ^ (mrow & 7)) << 4), a);
-          if (has_keep) {
-            // a[0]: rows (2q, 2q+1), chunk 2*cbk; a[1]: same rows, chunk 2*cbk + 1; a[2], a[3]: rows + 8
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const int chunk = 2 * cbk + (j & 1), rows = (j >> 1) * 2, c = chunk & 3;
-              const uint32_t sel = static_cast<uint32_t>(((4 + c) << 12) | ((4 + c) << 8) | (c << 4) | c);
-              a[j] &= __byte_perm(ksel[rows][chunk >> 2], ksel[rows + 1][chunk >> 2], sel);
-            }
-          }
-#pragma unroll
-          for (int n = 0; n < NB; ++n) mma_16816<kBf16>(acc[cbk][n], a, b[n]);
-        }
-      }
-      __syncwarp();  // also: every lane has read its keep rows before the ring slot is refilled (next trip's issue)
-      if (lane == 0) mbar_arrive(&empty[stage]);
-      if (++stage == STAGES) {
-        stage = 0;
-        phase ^= 1;
-      }
-    }
-    // acc fragment: (row c = cbk*16 + lane/4 [+8], col j = n*8 + (lane%4)*2 [+1]).
-    // The eight warps add their partial sums in warp order (named barrier 1 between turns):
-    // a fixed summation order keeps dA/dB bit-reproducible, which gradient-checkpoint
-    // recompute and the DDP equality tests rely on.
-    if constexpr (kWide) {
-      // every warp has left the ring: park the eight accumulators there, [warp][c][j ^ swz(c)] (the XOR spreads
-      // the eight rows of a store over the banks), then all threads add the eight copies in warp order
-      __syncthreads();
-      float* red = reinterpret_cast<float*>(smem);
-#pragma unroll
-      for (int cbk = 0; cbk < NCB; ++cbk)
-#pragma unroll
-        for (int n = 0; n < NB; ++n)
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const int c = cbk * 16 + (lane >> 2) + h * 8;
-            const int j = (n * 8 + (lane & 3) * 2) ^ ((c & 7) * (kRPad / 8));
-            *reinterpret_cast<float2*>(red + (warp * COLS + c) * kRPad + j) = make_float2(acc[cbk][n][2 * h], acc[cbk][n][2 * h + 1]);
-          }
-    } else
-    for (int turn = 0; turn < CP_CONSUMERS; ++turn) {
-      if (warp == turn) {
-#pragma unroll
-        for (int cbk = 0; cbk < NCB; ++cbk)
-#pragma unroll
-          for (int n = 0; n < NB; ++n)
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int c = cbk * 16 + (lane >> 2) + ((e >> 1) ? 8 : 0);
-              const int j = n * 8 + (lane & 3) * 2 + (e & 1);
-              sout[c * kRPad + j] += acc[cbk][n][e];
-            }
-      }
-      asm volatile("bar.sync 1, %0;" ::"n"(CP_CONSUMERS * 32) : "memory");
-    }
-  }
-  __syncthreads();
-  float* dst = p.partial + (static_cast<size_t>(blockIdx.y) * p.C + c0) * kRPad;
-  const int ncols = min(COLS, p.C - c0);
-  if constexpr (kWide) {
-    const float* red = reinterpret_cast<const float*>(smem);
-    for (int i = threadIdx.x; i < ncols * kRPad; i += THREADS) {
-      const int c = i / kRPad, jj = i % kRPad;
-      float s = 0.f;
-#pragma unroll
-      for (int w = 0; w < CP_CONSUMERS; ++w) s += red[(w * COLS + c) * kRPad + jj];
-      dst[c * kRPad + (jj ^ ((c & 7) * (kRPad / 8)))] = s;
-    }
-  } else {
-    for (int i = threadIdx.x; i < ncols * kRPad; i += THREADS) dst[i] = sout[i];
-  }
-
-  // The last CTA of this column tile to finish folds the splits, always in split order 0,1,2,...
-  // (the arrival order only decides WHO adds, never the order of the additions), applies the
-  // scale and writes the gradient: no separate reduction launch.
-  __shared__ int s_is_last;
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const unsigned int prev = atomicInc(p.counters + blockIdx.x, static_cast<unsigned int>(p.splits - 1));
-    s_is_last = (prev == static_cast<unsigned int>(p.splits - 1));
-  }
-  __syncthreads();
-  if (s_is_last) {
-    __threadfence();
-    for (int i = threadIdx.x; i < ncols * p.r; i += THREADS) {
-      const int cl = i / p.r, j = i - cl * p.r;
-      const float* src = p.partial + static_cast<size_t>(c0 + cl) * kRPad + j;
-      // split order 0,1,2,... as before, but four loads in flight at a time: with r = 64 and a dozen splits the
-      // serial chain of L2 round trips made this tail the longest part of the kernel (110 us for 768 -> 768)
-      const size_t sstride = static_cast<size_t>(p.C) * kRPad;
-      float acc = 0.f;
-      int sp = 0;
-      for (; sp + 4 <= p.splits; sp += 4) {
-        const float v0 = __ldcg(src + (sp + 0) * sstride), v1 = __ldcg(src + (sp + 1) * sstride);
-        const float v2 = __ldcg(src + (sp + 2) * sstride), v3 = __ldcg(src + (sp + 3) * sstride);
-        acc += v0;
-        acc += v1;
-        acc += v2;
-        acc += v3;
-      }
-      for (; sp < p.splits; ++sp) acc += __ldcg(src + sp * sstride);
-      float* o = p.out + static_cast<long long>(c0 + cl) * p.ld_c + static_cast<long long>(j) * p.ld_j;
-      *o = p.accumulate ? (*o + p.scale * acc) : (p.scale * acc);
     }
   }
 }
