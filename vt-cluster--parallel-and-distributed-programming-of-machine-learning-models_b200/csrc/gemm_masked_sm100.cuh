@@ -196,6 +196,7 @@ __global__ void __launch_bounds__(THREADS, 1)
     const int dtype = p.dtype;
     const int keep_ld = p.N >> 3;
     const float inv_keep = p.inv_keep;
+    const bool no_main = p.K1 == 0;  // K1 = 0: the masked rank-r term alone, D = keep/(1-p) .* (dH A)
     for (int tile = tile0; tile < num_tiles; tile += tile_step, ++it) {
       int m_blk, n_blk;
       tile_coords(tile, num_m, num_n, m_blk, n_blk);
@@ -236,7 +237,7 @@ __global__ void __launch_bounds__(THREADS, 1)
             for (int e = 0; e < 8; ++e) {
               const int i = q * 8 + e;
               const float w = ((kbits >> i) & 1u) ? inv_keep : 0.f;
-              o[e] = fmaf(__uint_as_float(t[i]), w, __uint_as_float(v[i]));
+              o[e] = fmaf(__uint_as_float(t[i]), w, no_main ? 0.f : __uint_as_float(v[i]));
             }
             uint4 pk;
             pk.x = pack2(o[0], o[1], dtype);

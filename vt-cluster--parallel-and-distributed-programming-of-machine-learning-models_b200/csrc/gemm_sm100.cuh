@@ -84,6 +84,10 @@ struct Params {
   // activation epilogue (kAct instantiation, un-adapted neighbours of the LoRA path): D = act(acc + bias)
   int act;      // kActNone / kActRelu / kActGeluNew
   int store_z;  // also store the pre-activation acc + bias through tmZ (gelu_new backward needs it)
+  // residual epilogue (plain kernel): D = acc + bias + R, R [M, res_ld] of the activation dtype; R may alias D
+  // (each tile is read by the CTA that later stores it)
+  const void* residual;
+  long long res_ld;
 };
 
 constexpr int kActNone = 0, kActRelu = 1, kActGeluNew = 2;
@@ -551,6 +555,33 @@ __global__ void __launch_bounds__(THREADS, 1)
         if (warp_rows_ok) {
           const int nchunks = (min(BN, p.N - n_blk * BN) + 31) / 32;  // warp-uniform, >= 1
           const uint32_t tbase = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + buf * BN;
+          // Residual rows come straight from global memory, 64 bytes per thread and chunk, requested one pair of
+          // chunks ahead (two register sets) so that an L2 round trip is covered by the chunk in between.
+          const bool has_res = p.residual != nullptr;
+          const uint16_t* rrow = reinterpret_cast<const uint16_t*>(p.residual) + static_cast<long long>(row) * p.res_ld;
+          auto load_res = [&](uint4 (&r)[4], int c) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              r[q] = (row < p.M && c + q * 8 < p.N) ? *reinterpret_cast<const uint4*>(rrow + c + q * 8)  // R may be D: no ld.nc
+                                                     : make_uint4(0u, 0u, 0u, 0u);
+          };
+          auto add_res = [&](uint32_t (&v)[32], const uint4 (&r)[4]) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint32_t w[4] = {r[q].x, r[q].y, r[q].z, r[q].w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float2 f = unpack2(w[e], dtype);
+                v[q * 8 + 2 * e] = __float_as_uint(__uint_as_float(v[q * 8 + 2 * e]) + f.x);
+                v[q * 8 + 2 * e + 1] = __float_as_uint(__uint_as_float(v[q * 8 + 2 * e + 1]) + f.y);
+              }
+            }
+          };
+          uint4 ra[4], rb[4];
+          if (has_res) {
+            load_res(ra, n_blk * BN);
+            load_res(rb, n_blk * BN + 32);
+          }
           auto emit = [&](uint32_t (&v)[32], int c, int h, uint8_t* sdst) {
             if (p.bias != nullptr) {
               const float4* bs = reinterpret_cast<const float4*>(bias_s + (c - n_blk * BN));
@@ -585,10 +616,18 @@ __global__ void __launch_bounds__(THREADS, 1)
             const bool has_b = ci + 1 < nchunks;
             tmem_ld_wait();
             if (has_b) tmem_ld_32x32b_x32(tbase + (ci + 1) * 32, vb);
+            if (has_res) {
+              add_res(va, ra);
+              if (ci + 2 < nchunks) load_res(ra, col0 + 64);
+            }
             emit(va, col0, 0, sdst);
             if (has_b) {
               tmem_ld_wait();
               if (ci + 2 < nchunks) tmem_ld_32x32b_x32(tbase + (ci + 2) * 32, va);
+              if (has_res) {
+                add_res(vb, rb);
+                if (ci + 3 < nchunks) load_res(rb, col0 + 96);
+              }
               emit(vb, col0 + 32, 1, sdst);
             }
             fence_proxy_async_smem();

@@ -484,6 +484,8 @@ struct GemmArgs {
   int act = 0;          // gemm::kActRelu / kActGeluNew: activation epilogue (frozen neighbours only)
   void* Z = nullptr;    // pre-activation output [M, N] (optional, act != 0)
   int64_t ldz = 0;
+  const void* residual = nullptr;  // [M, ldr] added in the plain epilogue (may be D itself)
+  int64_t ldr = 0;
 };
 
 // LORA_B200_GEMM=1cta forces the single-CTA tile shape (A/B testing); default: CTA pairs whenever
@@ -506,7 +508,9 @@ int launch_gemm_t(const CUtensorMap& tmA1, const CUtensorMap& tmB1, const CUtens
 
 // Backward with dropout, pair mode: 256 x 128 tiles with the rank-r product in its own TMEM accumulator
 // (gemm_masked_sm100.cuh).
-int launch_gemm_masked_pair(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, int sm_count, cudaStream_t stream) {
+// term_only: no main loop, D = keep/(1-p) .* (dH A) (first pass of the two-pass form below).
+int launch_gemm_masked_pair(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, int sm_count, cudaStream_t stream,
+                            bool term_only = false) {
   const int rp = rpad_of(g.masked_r);
   CUtensorMap tmA1, tmB1, tmA2, tmB2, tmD;
   if (make_tmap(&tmA1, g.A1, dtype, K1, M, g.lda1 ? g.lda1 : K1, gemm::BK, gemm::BM, CU_TENSOR_MAP_SWIZZLE_128B, "masked gemm A1")) return 1;
@@ -522,7 +526,7 @@ int launch_gemm_masked_pair(const GemmArgs& g, int64_t M, int64_t N, int64_t K1,
   gemm::MaskedParams p;
   p.M = (int)M;
   p.N = (int)N;
-  p.K1 = (int)K1;
+  p.K1 = term_only ? 0 : (int)K1;
   p.r_pad = rp;
   p.b_mn_major = g.b_mn_major;
   p.dtype = dtype;
@@ -550,10 +554,39 @@ bool use_masked_tmem(int rp, int64_t K1) {
   return rp >= 32 || K1 <= 1024;
 }
 
+// Wide ranks over a long contraction: the TMEM flavour's 128-column main loop costs more than a second pass over
+// the output.  Then the masked rank-r term is written first (TMEM kernel, K1 = 0) and the 256-column kernel adds
+// dY W on top of it through its residual epilogue.  Measured, r = 64, M = 16384, both passes together against the
+// single launch: dX of 2560 -> 10240 (K1 = 10240) 638 against 822 us, 2560 -> 2560 184 / 193, 10240 -> 2560 739 / 747,
+// 768 -> 2304 63 / 62; forced on at K1 = 768 (3072 -> 768) 129 against 85, hence the threshold.
+// LORA_B200_MASKED2=off|on forces the choice for A/B timing.
+bool masked_two_pass(int rp, int64_t K1) {
+  static const int forced = [] {
+    const char* e = getenv("LORA_B200_MASKED2");
+    return !e ? 0 : (strcmp(e, "off") == 0 ? 1 : (strcmp(e, "on") == 0 ? 2 : 0));
+  }();
+  if (forced) return forced == 2;
+  return rp >= 32 && K1 >= 2048;
+}
+
 int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, int sm_count, cudaStream_t stream) {
   const bool pair = pair_mode_allowed() && M > gemm::BM && sm_count >= 2;
-  if (pair && g.masked_r > 0 && !g.bias && !g.act && use_masked_tmem(rpad_of(g.masked_r), K1))
-    return launch_gemm_masked_pair(g, M, N, K1, dtype, sm_count, stream);
+  if (pair && g.masked_r > 0 && !g.bias && !g.act && use_masked_tmem(rpad_of(g.masked_r), K1)) {
+    if (!masked_two_pass(rpad_of(g.masked_r), K1)) return launch_gemm_masked_pair(g, M, N, K1, dtype, sm_count, stream);
+    // pass 1: D = keep/(1-p) .* (dH A) (the TMEM kernel without a main loop); pass 2: D = A1 B1 + D, 256-column tiles
+    if (launch_gemm_masked_pair(g, M, N, K1, dtype, sm_count, stream, true)) return 1;
+    GemmArgs g2{};
+    g2.A1 = g.A1;
+    g2.B1 = g.B1;
+    g2.lda1 = g.lda1;
+    g2.ldd = g.ldd;
+    g2.b_mn_major = g.b_mn_major;
+    g2.D = g.D;
+    g2.inv_keep = 1.f;
+    g2.residual = g.D;
+    g2.ldr = g.ldd ? g.ldd : N;
+    return launch_gemm(g2, M, N, K1, dtype, sm_count, stream);
+  }
   const uint32_t b_rows = pair ? gemm::BN / 2 : gemm::BN;  // rows of the B tile one CTA stages
   CUtensorMap tmA1, tmB1, tmA2, tmB2, tmD, tmZ;
   if (make_tmap(&tmA1, g.A1, dtype, K1, M, g.lda1 ? g.lda1 : K1, gemm::BK, gemm::BM, CU_TENSOR_MAP_SWIZZLE_128B, "gemm A1")) return 1;
@@ -591,6 +624,11 @@ int launch_gemm(const GemmArgs& g, int64_t M, int64_t N, int64_t K1, int dtype, 
   p.inv_keep = g.inv_keep;
   p.act = g.act;
   p.store_z = g.Z != nullptr;
+  p.residual = g.residual;
+  p.res_ld = g.ldr;
+  if (g.residual && (g.masked_r > 0 || g.act)) return fail("internal: the residual epilogue belongs to the plain kernel");
+  if (g.residual && ((g.ldr & 7) || (reinterpret_cast<uintptr_t>(g.residual) & 15)))
+    return fail("residual rows must be 16-byte aligned (row stride a multiple of 8 elements)");
 
   const int tile_m = pair ? 2 * gemm::BM : gemm::BM;
   const long long tiles = ((M + tile_m - 1) / tile_m) * ((N + gemm::BN - 1) / gemm::BN);
