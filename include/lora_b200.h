@@ -181,6 +181,19 @@ int lora_frozen_linear_bwd(const void* dY, int64_t lddy, const void* W, void* dX
                            int64_t N, int32_t dtype, int32_t w_is_KN, cudaStream_t stream);
 
 /*
+ * Frozen projection with a residual added in the GEMM epilogue:
+ *     Y[M,N] = X[M,K] W^T + bias + R[M,N]
+ * which is what the HF blocks compute as projection followed by `residual + hidden_states`
+ * (GPT2Block, OPTDecoderLayer) whenever no dropout sits between the two (eval, or dropout = 0).
+ * R has the activation dtype and row stride ldr (multiple of 8 elements, 16-byte aligned base); R may
+ * be Y itself (in-place accumulation).  The backward of the projection is lora_frozen_linear_bwd; the
+ * residual's gradient is dY itself.
+ */
+int lora_frozen_linear_add_fwd(const void* X, int64_t ldx, const void* W, const void* bias, const void* R, int64_t ldr,
+                               void* Y, int64_t ldy, int64_t M, int64_t K, int64_t N, int32_t dtype, int32_t w_is_KN,
+                               cudaStream_t stream);
+
+/*
  * Frozen projection with its activation applied in the GEMM epilogue: the
  * un-adapted `mlp.c_fc` + gelu_new of GPT-2 blocks (c_fc is no LoRA target at
  * finetune_lora_distilgpt2.py:100; HF runs addmm followed by ~8 elementwise kernels of

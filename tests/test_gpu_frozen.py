@@ -317,3 +317,52 @@ def test_committed_golden_vectors(pkg):
 def test_no_cpu_fallback(pkg):
     with pytest.raises(RuntimeError):
         pkg.frozen.fused_causal_lm_loss(torch.zeros(1, 4, 8), torch.zeros(1, 4, dtype=torch.long))
+
+
+@pytest.mark.parametrize("M,K,N,conv1d,dtype,bias", [(1024, 2560, 2560, False, torch.bfloat16, True),
+                                                     (300, 3072, 768, True, torch.bfloat16, True),
+                                                     (64, 768, 520, False, torch.float16, False)])
+def test_frozen_linear_residual_epilogue(pkg, M, K, N, conv1d, dtype, bias):
+    """residual + linear(x) with the add in the GEMM epilogue (lora_frozen_linear_add_fwd) against torch in fp32:
+    forward, dX and the residual's gradient; paired-CTA and single-CTA kernels, ragged N, Conv1D layout, fp16."""
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(M, K, generator=g).to(dtype).cuda().requires_grad_(True)
+    W = (torch.randn((K, N) if conv1d else (N, K), generator=g) * 0.02).to(dtype).cuda()
+    b = (torch.randn(N, generator=g) * 0.1).to(dtype).cuda() if bias else None
+    R = torch.randn(M, N, generator=g).to(dtype).cuda().requires_grad_(True)
+    y = pkg.frozen.frozen_linear_add(x, W, b, R, 1 if conv1d else 0)
+    dy = torch.randn(M, N, generator=g).to(dtype).cuda()
+    y.backward(dy)
+    xf, Rf = x.detach().float().requires_grad_(True), R.detach().float().requires_grad_(True)
+    Wf = W.float()
+    ref = (xf @ Wf if conv1d else xf @ Wf.t()) + (b.float() if bias else 0.0) + Rf
+    ref.backward(dy.float())
+
+    def relerr(a, r):
+        return float((a.float() - r).abs().max() / r.abs().max())
+
+    assert relerr(y, ref.detach()) < 2e-2
+    assert relerr(x.grad, xf.grad) < 2e-2
+    assert torch.equal(R.grad, dy)
+
+
+def test_frozen_linear_residual_in_place(pkg):
+    """R may be Y itself: the C entry point accumulates a projection onto a buffer that already holds a term."""
+    g = torch.Generator().manual_seed(4)
+    M, K, N = 512, 768, 768
+    x = torch.randn(M, K, generator=g).to(torch.bfloat16).cuda()
+    W = (torch.randn(N, K, generator=g) * 0.02).to(torch.bfloat16).cuda()
+    y = torch.randn(M, N, generator=g).to(torch.bfloat16).cuda()
+    ref = x.float() @ W.float().t() + y.float()
+    b = pkg.binding
+    rc = b.lib().lora_frozen_linear_add_fwd(y.new_empty(0).data_ptr() or None, K, None, None, None, N, None, N, M, K, N,
+                                            b.dtype_code(y.dtype), 0, None)
+    assert rc != 0 and "null pointer" in b.last_error()
+    import ctypes
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    rc = b.lib().lora_frozen_linear_add_fwd(x.data_ptr(), K, W.data_ptr(), None, y.data_ptr(), N, y.data_ptr(), N, M, K, N,
+                                            b.dtype_code(y.dtype), 0, st)
+    assert rc == 0, b.last_error()
+    torch.cuda.synchronize()
+    assert float((y.float() - ref).abs().max() / ref.abs().max()) < 2e-2
+

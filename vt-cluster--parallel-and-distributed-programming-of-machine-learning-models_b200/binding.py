@@ -47,6 +47,8 @@ _SIGNATURES = {
                                                            c_void_p]),
     "lora_frozen_linear_fwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64,
                                        c_int32, c_int32, c_void_p]),
+    "lora_frozen_linear_add_fwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int64,
+                                           c_int64, c_int64, c_int32, c_int32, c_void_p]),
     "lora_frozen_linear_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int32,
                                        c_int32, c_void_p]),
     "lora_frozen_linear_act_fwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int64,

@@ -922,6 +922,32 @@ int lora_frozen_linear_fwd(const void* X, int64_t ldx, const void* W, const void
   return launch_gemm(g, M, N, K, dtype, sms, stream);
 }
 
+int lora_frozen_linear_add_fwd(const void* X, int64_t ldx, const void* W, const void* bias, const void* R, int64_t ldr,
+                               void* Y, int64_t ldy, int64_t M, int64_t K, int64_t N, int32_t dtype, int32_t w_is_KN,
+                               cudaStream_t stream) {
+  g_err.clear();
+  if (M <= 0 || K <= 0 || N <= 0 || M > INT32_MAX || K > INT32_MAX || N > INT32_MAX) return fail("lora_frozen_linear_add_fwd: bad shape");
+  if (dtype != kDtypeBf16 && dtype != kDtypeFp16) return fail("dtype must be 0 (bf16) or 1 (fp16); fp32 is not supported");
+  if (!X || !W || !Y || !R) return fail("lora_frozen_linear_add_fwd: null pointer argument");
+  if (ldx < K || ldy < N || ldr < N || ldx % 8 || ldy % 8 || ldr % 8)
+    return fail("lora_frozen_linear_add_fwd: ldx/ldr/ldy must be >= K/N/N and multiples of 8 elements");
+  if ((w_is_KN ? N : K) % 8) return fail("lora_frozen_linear_add_fwd: the weight's row length (%s) must be a multiple of 8", w_is_KN ? "N" : "K");
+  int sms = 0;
+  if (device_setup(&sms)) return 1;
+  GemmArgs g{};
+  g.A1 = X;
+  g.lda1 = ldx;
+  g.B1 = W;
+  g.b_mn_major = w_is_KN ? 1 : 0;
+  g.D = Y;
+  g.ldd = ldy;
+  g.bias = bias;
+  g.inv_keep = 1.f;
+  g.residual = R;
+  g.ldr = ldr;
+  return launch_gemm(g, M, N, K, dtype, sms, stream);
+}
+
 int lora_frozen_linear_act_fwd(const void* X, int64_t ldx, const void* W, const void* bias, void* Y, int64_t ldy, void* Z,
                                int64_t ldz, int64_t M, int64_t K, int64_t N, int32_t act, int32_t dtype, int32_t w_is_KN,
                                cudaStream_t stream) {

@@ -97,6 +97,60 @@ class _FrozenLinearFn(torch.autograd.Function):
         return dX.view(x_shape), None, None, None
 
 
+class _FrozenLinearAddFn(torch.autograd.Function):
+    """y = x W^T + bias + residual with the add in the GEMM epilogue (lora_frozen_linear_add_fwd); dX through
+    lora_frozen_linear_bwd, the residual's gradient is dy itself."""
+
+    @staticmethod
+    @_on_device_of(1)
+    def forward(ctx, x, W, bias, residual, w_is_KN=0):
+        K = x.shape[-1]
+        N = W.shape[1] if w_is_KN else W.shape[0]
+        if N % 8 != 0:
+            raise ValueError("frozen_linear_add: out_features must be a multiple of 8")
+        x2 = x.reshape(-1, K)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        M = x2.shape[0]
+        r2 = residual.reshape(M, N)
+        if not r2.is_contiguous():
+            r2 = r2.contiguous()
+        if r2.dtype != x.dtype or r2.device != x.device:
+            raise ValueError("frozen_linear_add: residual must have the activation's dtype and device")
+        y = torch.empty((M, N), dtype=x.dtype, device=x.device)
+        rc = binding.lib().lora_frozen_linear_add_fwd(_p(x2), K, _p(W), _p(bias), _p(r2), N, _p(y), N, M, K, N,
+                                                      binding.dtype_code(x.dtype), w_is_KN, _stream())
+        binding._check(rc, "lora_frozen_linear_add_fwd")
+        ctx.save_for_backward(W)
+        ctx.meta = (x.shape, residual.shape, M, K, N, w_is_KN)
+        return y.view(*x.shape[:-1], N)
+
+    @staticmethod
+    @_on_device_of(1)
+    def backward(ctx, dy):
+        (W,) = ctx.saved_tensors
+        x_shape, r_shape, M, K, N, w_is_KN = ctx.meta
+        dy2 = dy.reshape(M, N)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dX = None
+        if ctx.needs_input_grad[0]:
+            dX = torch.empty((M, K), dtype=dy.dtype, device=dy.device)
+            rc = binding.lib().lora_frozen_linear_bwd(_p(dy2), N, _p(W), _p(dX), K, M, K, N,
+                                                      binding.dtype_code(dy.dtype), w_is_KN, _stream())
+            binding._check(rc, "lora_frozen_linear_bwd")
+            dX = dX.view(x_shape)
+        dR = dy2.view(r_shape) if ctx.needs_input_grad[3] else None
+        return dX, None, None, dR, None
+
+
+def frozen_linear_add(x, weight, bias, residual, w_is_KN: int = 0):
+    """residual + linear(x) for a frozen projection, the add done in the GEMM epilogue.  What
+    GPT2Block / OPTDecoderLayer compute as `residual + proj(h)` when no dropout sits between the two (eval, or
+    dropout = 0; with dropout > 0 the HF blocks drop the projection's output first, and the fusion does not apply)."""
+    return _FrozenLinearAddFn.apply(x, weight, bias, residual, w_is_KN)
+
+
 ACT_CODES = {None: 0, "relu": 1, "gelu_new": 2}
 
 
