@@ -110,16 +110,21 @@ __global__ void pack_adapters_kernel(const float* __restrict__ A, const float* _
 // are inefficient) and 7 slabs (147 CTAs, one per SM: too few warps per SM).
 __host__ __device__ constexpr int rp_slabs(int rpad) { return 4; }
 __host__ __device__ constexpr int rp_rows(int rpad) { return 16 * rp_slabs(rpad); }
-__host__ __device__ constexpr int rp_threads(int rpad) { return (2 * rp_slabs(rpad) + 1) * 32; }
+// Padded rank 64 needs ~123 registers per thread (32 accumulators, 16 B-fragment words).  ptxas sizes the register
+// file for the warp count rounded up to an even number, so nine warps cap a 2-CTA/SM kernel at 96; with EIGHT warps
+// (lane 0 of warp 0 also issues the TMA loads, one tile behind its own consumption) the cap is 128, two CTAs fit
+// per SM and the 256 CTAs of M = 16384 make one wave instead of two.
+__host__ __device__ constexpr bool rp_inline_producer(int rpad) { return rpad == 64; }
+__host__ __device__ constexpr int rp_threads(int rpad) { return (2 * rp_slabs(rpad) + (rp_inline_producer(rpad) ? 0 : 1)) * 32; }
 #ifndef LB_EXP_RP_MIN_CTAS
 #define LB_EXP_RP_MIN_CTAS 2  // measured: capping registers for a third CTA (72, spills) 64 us, uncapped 39 us
 #endif
 #ifndef LB_EXP_RP_STAGES
 #define LB_EXP_RP_STAGES 6
 #endif
-__host__ __device__ constexpr int rp_min_ctas(int rpad) { return rpad <= 16 ? LB_EXP_RP_MIN_CTAS : (rpad <= 32 ? 2 : 1); }
+__host__ __device__ constexpr int rp_min_ctas(int rpad) { return rpad <= 16 ? LB_EXP_RP_MIN_CTAS : 2; }
+__host__ __device__ constexpr int rp_stages(int rpad) { return rpad == 64 ? 5 : LB_EXP_RP_STAGES; }  // 64: 2 x 98 KiB per SM
 constexpr int RP_BK = 64;
-constexpr int RP_STAGES = LB_EXP_RP_STAGES;
 template <int kRPad>
 __host__ __device__ constexpr int rp_act_bytes() {
   return ((rp_rows(kRPad) * 128 + 1023) / 1024) * 1024;
@@ -130,7 +135,7 @@ __host__ __device__ constexpr int rp_slot_bytes() {
 }
 template <int kRPad>
 __host__ __device__ constexpr int rp_smem_bytes() {
-  return RP_STAGES * rp_slot_bytes<kRPad>() + rp_rows(kRPad) * kRPad * 4 + 1024 + 256;
+  return rp_stages(kRPad) * rp_slot_bytes<kRPad>() + rp_rows(kRPad) * kRPad * 4 + 1024 + 256;
 }
 
 struct RowProjParams {
@@ -165,6 +170,8 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
   constexpr int SLABS = rp_slabs(kRPad);
   constexpr int RP_BM = rp_rows(kRPad);
   constexpr int RP_CONSUMERS = 2 * SLABS;
+  constexpr int RP_STAGES = rp_stages(kRPad);
+  constexpr bool kInline = rp_inline_producer(kRPad);
   constexpr int RP_ACT_BYTES = rp_act_bytes<kRPad>();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -199,24 +206,23 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
                             static_cast<long long>(gridDim.x) * blockDim.x);
   }
 
-  if (warp == RP_CONSUMERS) {
-    if (lane == 0) {
-      uint32_t stage = 0, phase = 0;
-      for (int kb = 0; kb < nk; ++kb) {
-        mbar_wait(&empty[stage], phase ^ 1, 11);
-        uint8_t* act = smem + stage * SLOT;
-        mbar_arrive_expect_tx(&full[stage], RP_BM * 128 + (kDirectA ? 0 : kRPad * 128));
-        tma_load_2d(act, &tmAct, &full[stage], kb * RP_BK, m0);
-        if constexpr (!kDirectA) tma_load_2d(act + RP_ACT_BYTES, &tmP, &full[stage], kb * RP_BK, 0);
-        if (++stage == RP_STAGES) {
-          stage = 0;
-          phase ^= 1;
-        }
-      }
-    }
+  // column tile kb -> ring slot kb % RP_STAGES, once every consumer warp has released the slot's previous tile
+  auto produce = [&](int kb) {
+    const int st = kb % RP_STAGES;
+    mbar_wait(&empty[st], ((kb / RP_STAGES) & 1) ^ 1, 11);
+    uint8_t* act = smem + st * SLOT;
+    mbar_arrive_expect_tx(&full[st], RP_BM * 128 + (kDirectA ? 0 : kRPad * 128));
+    tma_load_2d(act, &tmAct, &full[st], kb * RP_BK, m0);
+    if constexpr (!kDirectA) tma_load_2d(act + RP_ACT_BYTES, &tmP, &full[st], kb * RP_BK, 0);
+  };
+  if (!kInline && warp == RP_CONSUMERS) {
+    if (lane == 0)
+      for (int kb = 0; kb < nk; ++kb) produce(kb);
     __syncwarp();
     return;
   }
+  if (kInline && warp == 0 && lane == 0)
+    for (int kb = 0; kb < min(nk, RP_STAGES); ++kb) produce(kb);
 
   const int slab = warp % SLABS;  // 16-row slab of the tile
   const int half = warp / SLABS;  // which two k16 steps of every tile this warp takes
@@ -331,6 +337,8 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
       if (kb0 + u >= nk) break;
+      // inline producer: the slot of the tile before this one is refilled here, when the other warps have (nearly) left it
+      if (kInline && warp == 0 && lane == 0 && kb0 + u >= 1 && kb0 + u - 1 + RP_STAGES < nk) produce(kb0 + u - 1 + RP_STAGES);
       mbar_wait(&full[stage], phase, 12);
       const uint32_t act_u = smem_u32(smem + stage * SLOT), pt_u = act_u + RP_ACT_BYTES;
 #pragma unroll
