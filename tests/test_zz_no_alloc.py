@@ -82,6 +82,18 @@ def test_static_scratch_matches_workspace_path_twice_in_a_row(pkg):
         assert _relerr(dB, 2 * dB_ref) < TOL
 
 
+def test_static_scratch_takes_fewer_splits_when_the_planned_ones_do_not_fit(pkg):
+    """M = 16384, N = 2560, r = 64: the planner wants 7 row splits x 2560 x 64 x 4 B = 4.6 MB, the block holds 4 MiB; the
+    call runs with 6 and gives the workspace path's result."""
+    M, K, N, r = 16384, 256, 2560, 64
+    dy, H, dB_ref, s = _reference_path(pkg, M, K, N, r, 5)
+    dB = torch.full((N, r), float("nan"), device="cuda")
+    rc = _grad_b_static(pkg, dy, H, dB, r, s)
+    assert rc == 0, pkg.binding.lib().lora_last_error().decode()
+    torch.cuda.synchronize()
+    assert torch.isfinite(dB).all() and _relerr(dB, dB_ref) < TOL
+
+
 def test_static_scratch_rejects_oversized_shapes(pkg):
     lib = pkg.binding.lib()
     M, N, r = 256, 20480, 64  # one row split x 20480 x 64 x 4 B = 5 MiB of partial sums > the 4 MiB block

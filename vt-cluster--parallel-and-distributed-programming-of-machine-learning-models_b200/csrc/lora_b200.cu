@@ -424,7 +424,7 @@ int launch_colproj_umma_t(const CUtensorMap (&tmAct)[2], const CUtensorMap (&tmS
 // Up to two column projections over the same M rows in ONE launch; each folds its own row splits
 // (last CTA per column tile), so no reduction kernel follows.
 int launch_colproj(const ColProjJob* jobs, int njobs, int64_t M, int r, int rp, int dtype, int accumulate,
-                   cudaStream_t stream) {
+                   cudaStream_t stream, const Split* given_plan = nullptr) {
   CUtensorMap tmAct[2], tmSmall[2];
   skinny::ColProjParams pp{};
   int64_t tiles[2] = {0, 0};
@@ -434,7 +434,8 @@ int launch_colproj(const ColProjJob* jobs, int njobs, int64_t M, int r, int rp, 
     masked[i] = jobs[i].keep != nullptr;
   }
   Split plan[2];
-  colproj_plan(M, njobs, tiles, masked, plan);
+  if (given_plan) plan[0] = plan[1] = *given_plan;  // single-problem callers that sized their scratch themselves
+  else colproj_plan(M, njobs, tiles, masked, plan);
   for (int i = 0; i < 2; ++i) {
     const ColProjJob& j = jobs[i < njobs ? i : 0];
     const Split& sp = plan[i < njobs ? i : 0];
@@ -882,7 +883,17 @@ int lora_linear_grad_b_static(const void* dY, const void* H, float* dB, int64_t 
   Split sp;
   colproj_plan(M, 1, &tiles, &no_mask, &sp);
   const size_t counter_bytes = align256(kMaxColTiles * sizeof(unsigned int));
-  const size_t need = counter_bytes + static_cast<size_t>(sp.splits) * static_cast<size_t>(N) * rp * sizeof(float);
+  // fewer row splits than planned when the planned number does not fit the built-in block (longer CTAs, same result
+  // up to the order of the fp32 additions); refused only when a single split does not fit
+  const size_t per_split = static_cast<size_t>(N) * rp * sizeof(float);
+  const size_t fit = (static_cast<size_t>(LORA_B200_STATIC_SCRATCH_BYTES) - counter_bytes) / per_split;
+  if (fit >= 1 && static_cast<size_t>(sp.splits) > fit) {
+    const int64_t m_tiles = (M + skinny::CP_BM - 1) / skinny::CP_BM;
+    const int64_t tiles_per = (m_tiles + static_cast<int64_t>(fit) - 1) / static_cast<int64_t>(fit);
+    sp.rows_per_split = static_cast<int>(tiles_per * skinny::CP_BM);
+    sp.splits = static_cast<int>((M + sp.rows_per_split - 1) / sp.rows_per_split);
+  }
+  const size_t need = counter_bytes + static_cast<size_t>(sp.splits) * per_split;
   if (need > static_cast<size_t>(LORA_B200_STATIC_SCRATCH_BYTES))
     return fail("lora_linear_grad_b_static: this shape needs %zu bytes of partial sums (M=%lld, N=%lld, padded rank %d) "
                 "but the built-in scratch holds %d; use lora_linear_bwd with a caller-provided workspace instead",
@@ -897,7 +908,7 @@ int lora_linear_grad_b_static(const void* dY, const void* H, float* dB, int64_t 
   // every one that is read was written earlier in the same call.
   ColProjJob job{dY, H, nullptr, reinterpret_cast<float*>(static_cast<unsigned char*>(scratch) + counter_bytes),
                  static_cast<unsigned int*>(scratch), dB, N, (long long)r, 1ll, scaling};
-  return launch_colproj(&job, 1, M, r, rp, dtype, accumulate, stream);
+  return launch_colproj(&job, 1, M, r, rp, dtype, accumulate, stream, &sp);
 }
 
 int lora_frozen_linear_fwd(const void* X, int64_t ldx, const void* W, const void* bias, void* Y, int64_t ldy, int64_t M,

@@ -114,7 +114,10 @@ __host__ __device__ constexpr int rp_rows(int rpad) { return 16 * rp_slabs(rpad)
 // file for the warp count rounded up to an even number, so nine warps cap a 2-CTA/SM kernel at 96; with EIGHT warps
 // (lane 0 of warp 0 also issues the TMA loads, one tile behind its own consumption) the cap is 128, two CTAs fit
 // per SM and the 256 CTAs of M = 16384 make one wave instead of two.
-__host__ __device__ constexpr bool rp_inline_producer(int rpad) { return rpad == 64; }
+#ifndef LB_EXP_RP_INLINE_ALL
+#define LB_EXP_RP_INLINE_ALL 0  // measured (scripts/gpu_r2_rp_variants2.sh): at padded rank 16 the inline producer LOSES
+#endif                          // (H with dropout 46.3 against 41.5 us, dH 17.0 / 15.7): the dedicated warp stays there
+__host__ __device__ constexpr bool rp_inline_producer(int rpad) { return LB_EXP_RP_INLINE_ALL || rpad == 64; }
 __host__ __device__ constexpr int rp_threads(int rpad) { return (2 * rp_slabs(rpad) + (rp_inline_producer(rpad) ? 0 : 1)) * 32; }
 #ifndef LB_EXP_RP_MIN_CTAS
 #define LB_EXP_RP_MIN_CTAS 2  // measured: capping registers for a third CTA (72, spills) 64 us, uncapped 39 us
