@@ -88,10 +88,12 @@ FWD_BWD_CASES = [
     (130, 776, 520, 8, 0.05, True, torch.bfloat16, True),  # its Conv1D twin
     (257, 520, 776, 16, 0.05, False, torch.float16, False),  # fp16, r = 16, M one past a 256-row pair tile
     (200, 2560, 2560, 24, 0.05, False, torch.bfloat16, True),  # r -> r_pad 32 masked epilogue (smem slice flavour)
-    # rank 64 / 32 over many row tiles and several row splits of the column projections (eight-warp wide form:
-    # inline TMA producer over more tiles than ring slots, accumulators folded through the ring)
+    # rank 64 / 32 over many row tiles and several row splits of the column projections (more tiles than ring
+    # slots, split fold by the last CTA) and a contraction >= 2048 in the backward: the two-pass masked dX
     (2400, 2560, 2560, 64, 0.05, False, torch.bfloat16, True),
     (1300, 768, 2304, 32, 0.05, True, torch.float16, True),
+    # more column tiles than SMs in the column projection (152 + 6 tiles of 128: one split each, two waves)
+    (256, 768, 19456, 8, 0.05, False, torch.bfloat16, False),
 ]
 
 
@@ -194,8 +196,9 @@ def test_merged_weight_equivalence(pkg):
     assert relerr(out["Y"], ym.float()) < TOL
 
 
-def test_accumulate_flag(pkg):
-    M, K, N, r, p = 256, 768, 768, 8, 0.05
+@pytest.mark.parametrize("M", [256, 100])  # two row splits folded by the last CTA / one split written by the epilogue
+def test_accumulate_flag(pkg, M):
+    K, N, r, p = 768, 768, 8, 0.05
     out, ref = _run_fwd_bwd(pkg, M, K, N, r, p, False, torch.bfloat16, True)
     d = out["d"]
     dA = out["dA"].clone()
