@@ -95,7 +95,8 @@ inline size_t tmap_hash(const TmapKey& k) {
   return static_cast<size_t>(h) & (kTmapSlots - 1);
 }
 
-// 2-D row-major tensor [outer, inner] of 16-bit elements, row stride in elements.
+// 2-D row-major tensor [outer, inner] of 16-bit elements (dtype 0 / 1) or fp32 (kTmapF32), row stride in elements.
+constexpr int kTmapF32 = 2;
 int make_tmap(CUtensorMap* tm, const void* ptr, int dtype, uint64_t inner, uint64_t outer, uint64_t row_stride_elems,
               uint32_t box_inner, uint32_t box_outer, CUtensorMapSwizzle sw, const char* what) {
   const TmapKey key{ptr, inner, outer, row_stride_elems, box_inner, box_outer, dtype, static_cast<int32_t>(sw)};
@@ -108,12 +109,14 @@ int make_tmap(CUtensorMap* tm, const void* ptr, int dtype, uint64_t inner, uint6
   EncodeTiledFn fn = encode_fn();
   if (!fn) return fail("cuTensorMapEncodeTiled not available from the driver");
   if ((reinterpret_cast<uintptr_t>(ptr) & 15u) != 0) return fail("%s: pointer not 16-byte aligned", what);
-  if ((row_stride_elems * 2) % 16 != 0) return fail("%s: row stride not a multiple of 16 bytes", what);
+  const uint64_t esz = dtype == kTmapF32 ? 4 : 2;
+  if ((row_stride_elems * esz) % 16 != 0) return fail("%s: row stride not a multiple of 16 bytes", what);
   cuuint64_t dims[2] = {inner, outer};
-  cuuint64_t strides[1] = {row_stride_elems * 2};
+  cuuint64_t strides[1] = {row_stride_elems * esz};
   cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
-  const CUtensorMapDataType dt = dtype == kDtypeBf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  const CUtensorMapDataType dt = dtype == kTmapF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                 : (dtype == kDtypeBf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16);
   CUresult r = fn(tm, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled(%s) failed with CUresult %d", what, (int)r);
@@ -353,8 +356,12 @@ int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out,
                    const DirectPack* direct = nullptr) {
   CUtensorMap tmAct, tmP;
   if (make_tmap(&tmAct, act, dtype, C, M, C, skinny::RP_BK, skinny::rp_rows(rp), CU_TENSOR_MAP_SWIZZLE_128B, "rowproj act")) return 1;
-  if (direct) tmP = tmAct;  // unused by the direct-A kernel
-  else if (make_tmap(&tmP, P, dtype, C, rp, C, skinny::RP_BK, rp, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj P")) return 1;
+  if (direct) {  // the fp32 master A [r, C]: boxes of 32 columns (one 128-byte swizzle row) x 8 or 16 rank rows
+    if (make_tmap(&tmP, direct->A, kTmapF32, C, direct->r, C, 32, direct->r <= 8 ? 8 : 16, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj A (fp32)"))
+      return 1;
+  } else if (make_tmap(&tmP, P, dtype, C, rp, C, skinny::RP_BK, rp, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj P")) {
+    return 1;
+  }
   skinny::RowProjParams rp_p{};
   rp_p.out = out;
   rp_p.keep_out = keep_out;
@@ -762,7 +769,8 @@ int lora_linear_fwd_devrng(const void* X, const void* W, const void* bias, const
 
   // Padded rank 16 (every adapter of the reference) with the masters at hand: the row projection reads A itself and
   // does the pack as a side job -- two launches per forward.  Wider ranks (or A = B = NULL) keep the pack launch.
-  const bool direct = A != nullptr && rp == 16 && phase_on(kPhaseRowProj) && phase_on(kPhasePack);
+  const bool direct = A != nullptr && rp == 16 && phase_on(kPhaseRowProj) && phase_on(kPhasePack) &&
+                      (reinterpret_cast<uintptr_t>(A) & 15u) == 0;  // TMA reads the master: 16-byte aligned base
   if (A != nullptr && !direct && phase_on(kPhasePack) && launch_pack(A, B, pk, w, K, N, r, scaling, dtype, stream)) return 1;
   if (phase_on(kPhaseRowProj)) {
     DirectPack dp;

@@ -29,6 +29,11 @@ __device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
 __device__ __forceinline__ void ldsm_x2(uint32_t addr, uint32_t (&r)[2]) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x2.shared.b16 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(addr));
 }
+__device__ __forceinline__ uint2 lds64(uint32_t saddr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(saddr));
+  return v;
+}
 template <bool kBf16>
 __device__ __forceinline__ void mma_16816(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
   if constexpr (kBf16) {
@@ -134,7 +139,9 @@ __host__ __device__ constexpr int rp_act_bytes() {
 }
 template <int kRPad>
 __host__ __device__ constexpr int rp_slot_bytes() {
-  return rp_act_bytes<kRPad>() + ((kRPad * 128 + 1023) / 1024) * 1024;
+  // the projection-matrix region: kRPad rows x 128 bytes of 16-bit P, or (padded rank 16, direct-A) two boxes of
+  // 8 / 16 rows x 32 fp32 columns straight from the master: 4 KiB covers both
+  return rp_act_bytes<kRPad>() + (kRPad == 16 ? 4096 : ((kRPad * 128 + 1023) / 1024) * 1024);
 }
 template <int kRPad>
 __host__ __device__ constexpr int rp_smem_bytes() {
@@ -153,9 +160,10 @@ struct RowProjParams {
   uint32_t thresh14;  // round(p * 16384)
   unsigned int* zero_words;  // optional: words CTA 0 clears (the column projections' arrival counters)
   int n_zero_words;
-  // kDirectA (forward, padded rank 16): the projection matrix is read straight from the fp32 master A [r, C]
-  // and the kernel also does the pack (A, B -> the four 16-bit layouts) as a side job for the kernels that follow,
-  // so the forward needs no pack launch.
+  // kDirectA (forward, padded rank 16): the projection matrix comes straight from the fp32 master A [r, C] (tmP is a
+  // tensor map over it: two 128-byte-swizzled boxes of 32 columns ride every stage, rows beyond r and columns beyond
+  // C arrive as zeros) and the kernel also does the pack (A, B -> the four 16-bit layouts) as a side job for the
+  // kernels that follow, so the forward needs no pack launch.
   const float* A32;
   const float* B32;  // [N, r]
   int r, N;
@@ -167,7 +175,8 @@ template <bool kBf16, int kRPad, bool kDirectA = false, int kNBE = 2>
 __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
     rowproj_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constant__ CUtensorMap tmP,
                    const RowProjParams p) {
-  static_assert(!kDirectA || kRPad == 16, "the direct-A path holds its B fragments in registers: padded rank 16 only");
+  static_assert(!kDirectA || kRPad == 16, "the direct-A path stages 8 / 16 fp32 rows per box: padded rank 16 only");
+  constexpr int A32_BOX_BYTES = 8 * kNBE * 128;  // direct-A: kNBE = 1 (r <= 8, the reference) loads 8 rows, else 16
   constexpr int SLOT = rp_slot_bytes<kRPad>();
   constexpr int NB = kRPad / 8;
   constexpr int SLABS = rp_slabs(kRPad);
@@ -214,9 +223,14 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
     const int st = kb % RP_STAGES;
     mbar_wait(&empty[st], ((kb / RP_STAGES) & 1) ^ 1, 11);
     uint8_t* act = smem + st * SLOT;
-    mbar_arrive_expect_tx(&full[st], RP_BM * 128 + (kDirectA ? 0 : kRPad * 128));
+    mbar_arrive_expect_tx(&full[st], RP_BM * 128 + (kDirectA ? 2 * A32_BOX_BYTES : kRPad * 128));
     tma_load_2d(act, &tmAct, &full[st], kb * RP_BK, m0);
-    if constexpr (!kDirectA) tma_load_2d(act + RP_ACT_BYTES, &tmP, &full[st], kb * RP_BK, 0);
+    if constexpr (!kDirectA) {
+      tma_load_2d(act + RP_ACT_BYTES, &tmP, &full[st], kb * RP_BK, 0);
+    } else {
+      tma_load_2d(act + RP_ACT_BYTES, &tmP, &full[st], kb * RP_BK, 0);
+      tma_load_2d(act + RP_ACT_BYTES + A32_BOX_BYTES, &tmP, &full[st], kb * RP_BK + 32, 0);
+    }
   };
   if (!kInline && warp == RP_CONSUMERS) {
     if (lane == 0)
@@ -264,42 +278,12 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
   // Two tiles per trip: their four Philox draws are independent dependency chains (10 rounds of a wide multiply
   // feeding a 3-input XOR each), issued back to back so that they hide one another's latency; with ~4 warps per
   // scheduler a single chain per warp leaves the issue slots idle (ncu: "wait" and "math pipe throttle" stalls).
-  constexpr int NBE_MAX = kDirectA ? kNBE : NB;  // kNBE = 1: r <= 8 (the reference), half the fragment registers
-  const int nbe = kDirectA ? min((p.r + 7) >> 3, kNBE) : NB;  // n-blocks (8 rank columns each) that are not all padding
-  // kDirectA: B fragments straight from the fp32 master, fetched one trip ahead (the loads of trip t+1 are issued
-  // after trip t's MMAs and packed to 16 bits at the top of trip t+1, so their latency hides under the Philox draws
-  // and only eight registers stay live across them): lane (g8, q) holds A[n*8 + g8][c .. c+1] and [c+8 .. c+9],
-  // c = 16-column step + 2q.
-  float2 braw[2][2][NBE_MAX][2];
-  auto load_braw = [&](int kb_first) {
-#pragma unroll
-    for (int u = 0; u < 2; ++u)
-#pragma unroll
-      for (int kk = 0; kk < 2; ++kk)
-#pragma unroll
-        for (int n = 0; n < NBE_MAX; ++n)
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const int j = n * 8 + g8, c = (kb_first + u) * RP_BK + (half * 2 + kk) * 16 + h * 8 + 2 * q;
-            braw[u][kk][n][h] = (n < nbe && j < p.r && c < p.C)
-                                    ? __ldg(reinterpret_cast<const float2*>(p.A32 + static_cast<size_t>(j) * p.C + c))
-                                    : make_float2(0.f, 0.f);
-          }
-  };
-  if constexpr (kDirectA) load_braw(0);
+  // kDirectA: B fragments from the fp32 tile of A in the stage: lane (g8, q) needs A[n*8 + g8][c .. c+1] and
+  // [c+8 .. c+9], c = 16-column step + 2q -- two 8-byte shared loads (the 128-byte swizzle spreads the eight rows of
+  // a load over the banks) packed to 16 bits.  (First written with the fragments fetched from global memory into
+  // registers one trip ahead: the L2 round trip sat on the pack, 11 % of the kernel's stall samples at M = 16384
+  // and most of the time of a lone warp at small M.)
   for (int kb0 = 0; kb0 < nk; kb0 += 2) {
-    uint32_t bpk[2][2][NBE_MAX][2];
-    if constexpr (kDirectA) {
-#pragma unroll
-      for (int u = 0; u < 2; ++u)
-#pragma unroll
-        for (int kk = 0; kk < 2; ++kk)
-#pragma unroll
-          for (int n = 0; n < NBE_MAX; ++n)
-#pragma unroll
-            for (int h = 0; h < 2; ++h)
-              bpk[u][kk][n][h] = pack2(braw[u][kk][n][h].x, braw[u][kk][n][h].y, kBf16 ? kDtypeBf16 : kDtypeFp16);
-    }
     uint32_t kmask[2][2][4];
     if (p.dropout) {
       uint32_t kw[2][2];
@@ -356,9 +340,13 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
         for (int n = 0; n < NB; ++n) {
           uint32_t b[2];
           if constexpr (kDirectA) {
-            if (n >= nbe || n >= NBE_MAX) continue;  // warp-uniform: all-padding rank columns contribute nothing
-            b[0] = bpk[u][kk][n < NBE_MAX ? n : 0][0];
-            b[1] = bpk[u][kk][n < NBE_MAX ? n : 0][1];
+            if (n >= kNBE) continue;  // all-padding rank columns contribute nothing
+            const int arow = n * 8 + g8;
+            const uint32_t abox = pt_u + (ks >> 1) * A32_BOX_BYTES + arow * 128 + (q & 1) * 8;
+            const int ch = (ks & 1) * 4 + (q >> 1);  // 16-byte chunk of columns c .. c+1; columns c+8 .. c+9 are two chunks on
+            const uint2 lo = lds64(abox + ((ch ^ (arow & 7)) << 4)), hi = lds64(abox + (((ch + 2) ^ (arow & 7)) << 4));
+            b[0] = pack2(__uint_as_float(lo.x), __uint_as_float(lo.y), kBf16 ? kDtypeBf16 : kDtypeFp16);
+            b[1] = pack2(__uint_as_float(hi.x), __uint_as_float(hi.y), kBf16 ? kDtypeBf16 : kDtypeFp16);
           } else {
             const int prow = n * 8 + b_row;
             ldsm_x2(pt_u + prow * 128 + (((ks * 2 + b_hi) ^ (prow & 7)) << 4), b);
@@ -373,7 +361,6 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
         phase ^= 1;
       }
     }
-    if constexpr (kDirectA) load_braw(kb0 + 2);  // columns beyond C come back as zeros
   }
 
   // acc fragment: (row = lane/4 [+8], col = n*8 + (lane%4)*2 [+1]); half 1 hands its partial
