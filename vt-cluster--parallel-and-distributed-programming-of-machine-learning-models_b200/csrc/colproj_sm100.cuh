@@ -1,15 +1,16 @@
-// Column projections of the backward at padded rank 32 / 64 on the tcgen05 tensor cores:
+// Column projections of the backward on the tcgen05 tensor cores (every padded rank: 16 / 32 / 64):
 //     dB = s dY^T H        dA = dH^T drop(X)          (torch autograd over peft's lora_B / lora_A linears)
 // i.e. out[c, j] = sum_m keep(m, c) Act[m, c] Small[m, j] with Act = dY or X ([M, C], 16-bit), Small = H or dH
-// ([M, r_pad], 16-bit).  The warp-MMA kernel of skinny.cuh carries these at padded rank 16, where the launch is
-// HBM-bound; at rank 64 its 128 accumulator registers per thread leave eight warps per SM and the launch ran at
-// 12 % of the legacy HMMA rate (r02 profile).  Here the reduction over the rows m is ONE accumulator in tensor
-// memory per CTA:  D[128 columns c, r_pad] (fp32, r_pad TMEM columns) += Act_tile^T [128 c x 128 m] Small_tile
-// [128 m x r_pad], eight UMMA 128 x r_pad x 16 per 128-row tile.  Both operands have the reduction dimension m as
-// their SLOW dimension in memory, so both are "MN-major" UMMA operands straight out of the TMA boxes:
+// ([M, r_pad], 16-bit).  One pass over dY and one over X: HBM-bound by design.  The reduction over the rows m is ONE
+// accumulator in tensor memory per CTA:  D[128 columns c, r_pad] (fp32, r_pad TMEM columns) += Act_tile^T
+// [128 c x 128 m] Small_tile [128 m x r_pad], eight UMMA 128 x r_pad x 16 per 128-row tile.  Both operands have
+// the reduction dimension m as their SLOW dimension in memory, so both are "MN-major" UMMA operands straight out of
+// the TMA boxes:
 //     Act  : two boxes of 64 columns x 128 rows, 128-byte swizzle  (LBO = one box, SBO = 8 rows)
-//     Small: one box of r_pad columns x 128 rows, swizzle = row bytes (128 / 64)
-// Warp roles (320 threads, one CTA per SM, 4-slot ring of 48 / 40 KiB):
+//     Small: one box of r_pad columns x 128 rows, swizzle = row bytes (32 / 64 / 128)
+// (The warp-mma.sync kernel this replaced in round 2 was HBM-bound at padded rank 16 but ran at 12 % of the legacy
+// HMMA rate at rank 64: 128 accumulator registers per thread, spilled, eight warps per SM)
+// Warp roles (320 threads, one CTA per SM, 4-slot ring of 36 / 40 / 48 KiB):
 //     warp 0   TMA producer
 //     warp 1   TMEM allocation + the single MMA-issuing thread
 //     warps 2-9  dropout (dA only): AND the keep-bits into the Act tile in shared memory before the MMA reads it
@@ -17,9 +18,9 @@
 //               p = 0.05 -- are left alone)
 //     warps 2-5  then the epilogue: TMEM -> registers -> the split's partial sums in global memory (or, with a
 //               single row split, straight to the gradient)
-// grid = (column tiles of 128, row splits, problems).  The last CTA of a column tile to finish folds the row
-// splits in split order (same scheme and the same arrival counters as skinny::colproj_kernel): no reduction launch,
-// bit-reproducible.
+// grid = (column tiles of 128, row splits, problems).  The last CTA of a column tile to finish (self-resetting
+// atomicInc arrival counter) folds the row splits in split order: no reduction launch, bit-reproducible.
+// Every tensor map covers this GPU's memory.
 #pragma once
 
 #include "skinny.cuh"

@@ -307,12 +307,13 @@ __host__ __device__ __forceinline__ PhiloxKeys philox_round_keys(uint64_t seed) 
 #ifdef __CUDACC__
 // thresh14 -> the packed-half constant dropout_fragment_masks compares against
 __host__ __device__ __forceinline__ uint32_t dropout_thresh_half2(uint32_t thresh14) {
-  return (thresh14 + 0x0400u) * 0x00010001u;
+  return thresh14 * 0x00010001u;
 }
 // One draw for the calling lane: mask[w] is the AND-mask (0xFFFF per surviving 16-bit element) of
 // A-fragment register w of an m16n8k16 MMA over the block whose counter base is (g_lo, g_hi) + lane.
-// The 14-bit lanes, offset by 0x0400, are all positive NORMAL fp16 bit patterns (0x0400..0x43FF),
-// whose floating-point order equals their integer order: one HSET2 per word gives both masks.
+// The 14-bit lanes are non-negative finite fp16 bit patterns (0x0000..0x3FFF: zero, subnormals, normals below 2),
+// whose floating-point order equals their integer order, and set.ge.f16x2 without .ftz honours subnormals:
+// one HSET2 per word gives both masks.
 // Returns the eight keep-bits of the draw, bit 2w + h = element h of register w.
 __device__ __forceinline__ uint32_t dropout_fragment_masks(uint32_t g_lo, uint32_t g_hi, uint32_t off_lo,
                                                            uint32_t off_hi, const PhiloxKeys& rk, uint32_t thresh_h2,
@@ -345,7 +346,7 @@ __device__ __forceinline__ uint32_t dropout_fragment_masks(uint32_t g_lo, uint32
   const __half2 th = *reinterpret_cast<const __half2*>(&thresh_h2);
 #pragma unroll
   for (int w = 0; w < 4; ++w) {
-    const uint32_t x = (r[w] & 0x3FFF3FFFu) + 0x04000400u;
+    const uint32_t x = r[w] & 0x3FFF3FFFu;
     mask[w] = __hge2_mask(*reinterpret_cast<const __half2*>(&x), th);
   }
   // byte 0 of each half-word mask -> one bit each: (m0.lo, m0.hi, m1.lo, m1.hi | m2.lo, ...)
