@@ -194,17 +194,22 @@ int device_setup(int* sm_count) {
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false, false, true>, gemm::SMEM_BYTES));
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false, true, true>, gemm::SMEM_BYTES));
     CUDA_TRY(opt_in_smem(gemm::gemm_masked_kernel, gemm::SMEM_BYTES));
-#define OPT_IN_SKINNY(BF, RP) CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP>, skinny::rp_smem_bytes<RP>()));
+#define OPT_IN_SKINNY(BF, RP)                                                                                       \
+  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP, false, 2, 4>, skinny::rp_smem_bytes<RP, 4>()));               \
+  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP, false, 2, 2>, skinny::rp_smem_bytes<RP, 2>()));               \
+  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP, false, 2, 1>, skinny::rp_smem_bytes<RP, 1>()));
+#define OPT_IN_DIRECT(BF, NBE)                                                                                      \
+  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, 16, true, NBE, 4>, skinny::rp_smem_bytes<16, 4>()));              \
+  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, 16, true, NBE, 2>, skinny::rp_smem_bytes<16, 2>()));              \
+  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, 16, true, NBE, 1>, skinny::rp_smem_bytes<16, 1>()));
     CUDA_TRY(opt_in_smem(skinny::colproj_umma_kernel<16>, skinny::cu_smem_bytes<16>()));
     CUDA_TRY(opt_in_smem(skinny::colproj_umma_kernel<32>, skinny::cu_smem_bytes<32>()));
     CUDA_TRY(opt_in_smem(skinny::colproj_umma_kernel<64>, skinny::cu_smem_bytes<64>()));
-    CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<true, 16, true, 1>, skinny::rp_smem_bytes<16>()));
-    CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<false, 16, true, 1>, skinny::rp_smem_bytes<16>()));
-    CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<true, 16, true, 2>, skinny::rp_smem_bytes<16>()));
-    CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<false, 16, true, 2>, skinny::rp_smem_bytes<16>()));
+    OPT_IN_DIRECT(true, 1) OPT_IN_DIRECT(false, 1) OPT_IN_DIRECT(true, 2) OPT_IN_DIRECT(false, 2)
     OPT_IN_SKINNY(true, 16) OPT_IN_SKINNY(true, 32) OPT_IN_SKINNY(true, 64)
     OPT_IN_SKINNY(false, 16) OPT_IN_SKINNY(false, 32) OPT_IN_SKINNY(false, 64)
 #undef OPT_IN_SKINNY
+#undef OPT_IN_DIRECT
     d.sm_count = sms;
     d.ready.store(1, std::memory_order_release);
   }
@@ -327,13 +332,22 @@ int launch_pack(const float* A, const float* B, uint8_t* pk, const Packed& w, in
   return 0;
 }
 
+template <bool BF, int RP, bool DIRECT, int NBE, int SLABS>
+int launch_rowproj_s(const CUtensorMap& tmAct, const CUtensorMap& tmP, const skinny::RowProjParams& p,
+                     cudaStream_t stream) {
+  const int grid = (p.M + skinny::rp_rows(SLABS) - 1) / skinny::rp_rows(SLABS);
+  CUDA_TRY(launch_pdl(skinny::rowproj_kernel<BF, RP, DIRECT, NBE, SLABS>, dim3(grid), dim3(skinny::rp_threads(RP, SLABS)),
+                      skinny::rp_smem_bytes<RP, SLABS>(), stream, 1, tmAct, tmP, p));
+  return 0;
+}
+// 16-row slabs per CTA by M (skinny::rp_slabs_for): the tensor map of the activation was built for the same box
 template <bool BF, int RP, bool DIRECT = false, int NBE = 2>
 int launch_rowproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmP, const skinny::RowProjParams& p,
                      cudaStream_t stream) {
-  const int grid = (p.M + skinny::rp_rows(RP) - 1) / skinny::rp_rows(RP);
-  CUDA_TRY(launch_pdl(skinny::rowproj_kernel<BF, RP, DIRECT, NBE>, dim3(grid), dim3(skinny::rp_threads(RP)),
-                      skinny::rp_smem_bytes<RP>(), stream, 1, tmAct, tmP, p));
-  return 0;
+  const int slabs = skinny::rp_slabs_for(p.M);
+  if (slabs == 4) return launch_rowproj_s<BF, RP, DIRECT, NBE, 4>(tmAct, tmP, p, stream);
+  if (slabs == 2) return launch_rowproj_s<BF, RP, DIRECT, NBE, 2>(tmAct, tmP, p, stream);
+  return launch_rowproj_s<BF, RP, DIRECT, NBE, 1>(tmAct, tmP, p, stream);
 }
 
 // Forward with padded rank 16 and the fp32 masters at hand: the row projection reads A directly and packs A, B
@@ -355,7 +369,9 @@ int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out,
                    const uint64_t* offset_dev = nullptr, unsigned int* zero_words = nullptr, int n_zero_words = 0,
                    const DirectPack* direct = nullptr) {
   CUtensorMap tmAct, tmP;
-  if (make_tmap(&tmAct, act, dtype, C, M, C, skinny::RP_BK, skinny::rp_rows(rp), CU_TENSOR_MAP_SWIZZLE_128B, "rowproj act")) return 1;
+  if (make_tmap(&tmAct, act, dtype, C, M, C, skinny::RP_BK, skinny::rp_rows(skinny::rp_slabs_for(M)), CU_TENSOR_MAP_SWIZZLE_128B,
+                "rowproj act"))
+    return 1;
   if (direct) {  // the fp32 master A [r, C]: boxes of 32 columns (one 128-byte swizzle row) x 8 or 16 rank rows
     if (make_tmap(&tmP, direct->A, kTmapF32, C, direct->r, C, 32, direct->r <= 8 ? 8 : 16, CU_TENSOR_MAP_SWIZZLE_128B, "rowproj A (fp32)"))
       return 1;

@@ -113,8 +113,12 @@ __global__ void pack_adapters_kernel(const float* __restrict__ A, const float* _
 // 16-row slabs per CTA.  Measured on B200 (M = 16384, C = 2560, r_pad 16, round 1): 4 slabs (64 rows,
 // 256 CTAs) beat 1 slab (1024 small CTAs: every CTA re-reads the P tiles from L2 and 2 KiB TMA boxes
 // are inefficient) and 7 slabs (147 CTAs, one per SM: too few warps per SM).
-__host__ __device__ constexpr int rp_slabs(int rpad) { return 4; }
-__host__ __device__ constexpr int rp_rows(int rpad) { return 16 * rp_slabs(rpad); }
+// kSlabs is a template parameter: 4 whenever that fills the GPU (M >= 148 x 64 rows), else 2 or 1 -- the kernel is
+// bound by the integer pipes of the SMs that hold a CTA (section 4.2 of DESIGN.md), so at M = 4096 four-slab CTAs
+// put the whole generator on 64 of the 148 SMs (35.7 us, the time of M = 16384).
+__host__ __device__ constexpr int rp_rows(int slabs) { return 16 * slabs; }
+// slabs for M rows: the largest of 4 / 2 / 1 that still gives every SM a CTA
+inline int rp_slabs_for(long long M) { return M >= 148 * 64 ? 4 : (M >= 148 * 32 ? 2 : 1); }
 // Padded rank 64 needs ~123 registers per thread (32 accumulators, 16 B-fragment words).  ptxas sizes the register
 // file for the warp count rounded up to an even number, so nine warps cap a 2-CTA/SM kernel at 96; with EIGHT warps
 // (lane 0 of warp 0 also issues the TMA loads, one tile behind its own consumption) the cap is 128, two CTAs fit
@@ -123,7 +127,7 @@ __host__ __device__ constexpr int rp_rows(int rpad) { return 16 * rp_slabs(rpad)
 #define LB_EXP_RP_INLINE_ALL 0  // measured (scripts/gpu_r2_rp_variants2.sh): at padded rank 16 the inline producer LOSES
 #endif                          // (H with dropout 46.3 against 41.5 us, dH 17.0 / 15.7): the dedicated warp stays there
 __host__ __device__ constexpr bool rp_inline_producer(int rpad) { return LB_EXP_RP_INLINE_ALL || rpad == 64; }
-__host__ __device__ constexpr int rp_threads(int rpad) { return (2 * rp_slabs(rpad) + (rp_inline_producer(rpad) ? 0 : 1)) * 32; }
+__host__ __device__ constexpr int rp_threads(int rpad, int slabs) { return (2 * slabs + (rp_inline_producer(rpad) ? 0 : 1)) * 32; }
 #ifndef LB_EXP_RP_MIN_CTAS
 #define LB_EXP_RP_MIN_CTAS 2  // measured: capping registers for a third CTA (72, spills) 64 us, uncapped 39 us
 #endif
@@ -133,19 +137,19 @@ __host__ __device__ constexpr int rp_threads(int rpad) { return (2 * rp_slabs(rp
 __host__ __device__ constexpr int rp_min_ctas(int rpad) { return rpad <= 16 ? LB_EXP_RP_MIN_CTAS : 2; }
 __host__ __device__ constexpr int rp_stages(int rpad) { return rpad == 64 ? 5 : LB_EXP_RP_STAGES; }  // 64: 2 x 98 KiB per SM
 constexpr int RP_BK = 64;
-template <int kRPad>
+template <int kSlabs>
 __host__ __device__ constexpr int rp_act_bytes() {
-  return ((rp_rows(kRPad) * 128 + 1023) / 1024) * 1024;
+  return ((rp_rows(kSlabs) * 128 + 1023) / 1024) * 1024;
 }
-template <int kRPad>
+template <int kRPad, int kSlabs>
 __host__ __device__ constexpr int rp_slot_bytes() {
   // the projection-matrix region: kRPad rows x 128 bytes of 16-bit P, or (padded rank 16, direct-A) two boxes of
   // 8 / 16 rows x 32 fp32 columns straight from the master: 4 KiB covers both
-  return rp_act_bytes<kRPad>() + (kRPad == 16 ? 4096 : ((kRPad * 128 + 1023) / 1024) * 1024);
+  return rp_act_bytes<kSlabs>() + (kRPad == 16 ? 4096 : ((kRPad * 128 + 1023) / 1024) * 1024);
 }
-template <int kRPad>
+template <int kRPad, int kSlabs>
 __host__ __device__ constexpr int rp_smem_bytes() {
-  return rp_stages(kRPad) * rp_slot_bytes<kRPad>() + rp_rows(kRPad) * kRPad * 4 + 1024 + 256;
+  return rp_stages(kRPad) * rp_slot_bytes<kRPad, kSlabs>() + rp_rows(kSlabs) * kRPad * 4 + 1024 + 256;
 }
 
 struct RowProjParams {
@@ -171,20 +175,20 @@ struct RowProjParams {
   void *a16, *a16t, *sb16, *sb16t;
 };
 
-template <bool kBf16, int kRPad, bool kDirectA = false, int kNBE = 2>
-__global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
+template <bool kBf16, int kRPad, bool kDirectA = false, int kNBE = 2, int kSlabs = 4>
+__global__ void __launch_bounds__(rp_threads(kRPad, kSlabs), rp_min_ctas(kRPad))
     rowproj_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constant__ CUtensorMap tmP,
                    const RowProjParams p) {
   static_assert(!kDirectA || kRPad == 16, "the direct-A path stages 8 / 16 fp32 rows per box: padded rank 16 only");
   constexpr int A32_BOX_BYTES = 8 * kNBE * 128;  // direct-A: kNBE = 1 (r <= 8, the reference) loads 8 rows, else 16
-  constexpr int SLOT = rp_slot_bytes<kRPad>();
+  constexpr int SLOT = rp_slot_bytes<kRPad, kSlabs>();
   constexpr int NB = kRPad / 8;
-  constexpr int SLABS = rp_slabs(kRPad);
-  constexpr int RP_BM = rp_rows(kRPad);
+  constexpr int SLABS = kSlabs;
+  constexpr int RP_BM = rp_rows(kSlabs);
   constexpr int RP_CONSUMERS = 2 * SLABS;
   constexpr int RP_STAGES = rp_stages(kRPad);
   constexpr bool kInline = rp_inline_producer(kRPad);
-  constexpr int RP_ACT_BYTES = rp_act_bytes<kRPad>();
+  constexpr int RP_ACT_BYTES = rp_act_bytes<kSlabs>();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   float* sred = reinterpret_cast<float*>(smem + RP_STAGES * SLOT);  // [64 rows][kRPad] pair reduction
@@ -292,16 +296,26 @@ __global__ void __launch_bounds__(rp_threads(kRPad), rp_min_ctas(kRPad))
 #pragma unroll
         for (int kk = 0; kk < 2; ++kk) {
           const uint64_t g = gbase + static_cast<uint64_t>((kb0 + u) * 4 + kk) * 32ull;
-          const uint32_t b = dropout_fragment_masks(static_cast<uint32_t>(g), static_cast<uint32_t>(g >> 32), off_lo,
-                                                    off_hi, rk, thresh2, kmask[u][kk]);
-          // 2-bit field of register w -> byte w of a word, at bit 2q; the quad's four pieces OR into whole bytes:
-          // byte 0 = (row g8, chunk 0), byte 1 = (row g8+8, chunk 0), byte 2 = (g8, chunk 1), byte 3 = (g8+8, chunk 1)
-          uint32_t t = (b * 0x1001u) & 0x000F000Fu;
-          t = ((t * 0x41u) & 0x03030303u) << (2 * q);
-          t |= __shfl_xor_sync(0xFFFFFFFFu, t, 1);
-          t |= __shfl_xor_sync(0xFFFFFFFFu, t, 2);
-          kw[u][kk] = t;
+          kw[u][kk] = dropout_fragment_masks(static_cast<uint32_t>(g), static_cast<uint32_t>(g >> 32), off_lo, off_hi, rk,
+                                             thresh2, kmask[u][kk]);
         }
+      // The four draws above are pure arithmetic and independent; the shuffles come only now, all together: a
+      // shuffle between two draws keeps the compiler from interleaving their dependency chains.
+      // 2-bit field of register w -> byte w of a word, at bit 2q; the quad's four pieces OR into whole bytes:
+      // byte 0 = (row g8, chunk 0), byte 1 = (row g8+8, chunk 0), byte 2 = (g8, chunk 1), byte 3 = (g8+8, chunk 1)
+#pragma unroll
+      for (int u = 0; u < 2; ++u)
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk) {
+          uint32_t t = (kw[u][kk] * 0x1001u) & 0x000F000Fu;
+          kw[u][kk] = ((t * 0x41u) & 0x03030303u) << (2 * q);
+        }
+#pragma unroll
+      for (int o = 1; o <= 2; o <<= 1)
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+#pragma unroll
+          for (int kk = 0; kk < 2; ++kk) kw[u][kk] |= __shfl_xor_sync(0xFFFFFFFFu, kw[u][kk], o);
       if (kstore) {
         // this lane's row: chunk bytes (kk 0: c0, c1; kk 1: c0, c1) of the warp's half tile
         const uint32_t sel = (q & 1) ? 0x7531u : 0x6420u;
