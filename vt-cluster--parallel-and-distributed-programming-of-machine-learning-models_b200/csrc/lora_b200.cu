@@ -195,13 +195,13 @@ int device_setup(int* sm_count) {
     CUDA_TRY(opt_in_smem(gemm::gemm_lora_kernel<false, true, true>, gemm::SMEM_BYTES));
     CUDA_TRY(opt_in_smem(gemm::gemm_masked_kernel, gemm::SMEM_BYTES));
 #define OPT_IN_SKINNY(BF, RP)                                                                                       \
-  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP, false, 2, 4>, skinny::rp_smem_bytes<RP, 4>()));               \
-  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP, false, 2, 2>, skinny::rp_smem_bytes<RP, 2>()));               \
-  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP, false, 2, 1>, skinny::rp_smem_bytes<RP, 1>()));
+  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP, false, 2, 4>, skinny::rp_smem_optin<RP, 4>()));               \
+  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP, false, 2, 2>, skinny::rp_smem_optin<RP, 2>()));               \
+  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP, false, 2, 1>, skinny::rp_smem_optin<RP, 1>()));
 #define OPT_IN_DIRECT(BF, NBE)                                                                                      \
-  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, 16, true, NBE, 4>, skinny::rp_smem_bytes<16, 4>()));              \
-  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, 16, true, NBE, 2>, skinny::rp_smem_bytes<16, 2>()));              \
-  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, 16, true, NBE, 1>, skinny::rp_smem_bytes<16, 1>()));
+  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, 16, true, NBE, 4>, skinny::rp_smem_optin<16, 4>()));              \
+  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, 16, true, NBE, 2>, skinny::rp_smem_optin<16, 2>()));              \
+  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, 16, true, NBE, 1>, skinny::rp_smem_optin<16, 1>()));
     CUDA_TRY(opt_in_smem(skinny::colproj_umma_kernel<16>, skinny::cu_smem_bytes<16>()));
     CUDA_TRY(opt_in_smem(skinny::colproj_umma_kernel<32>, skinny::cu_smem_bytes<32>()));
     CUDA_TRY(opt_in_smem(skinny::colproj_umma_kernel<64>, skinny::cu_smem_bytes<64>()));
@@ -336,8 +336,14 @@ template <bool BF, int RP, bool DIRECT, int NBE, int SLABS>
 int launch_rowproj_s(const CUtensorMap& tmAct, const CUtensorMap& tmP, const skinny::RowProjParams& p,
                      cudaStream_t stream) {
   const int grid = (p.M + skinny::rp_rows(SLABS) - 1) / skinny::rp_rows(SLABS);
+  // Fewer CTAs than SMs: ask for more than half an SM's shared memory so that every CTA gets an SM of its own.  The
+  // hardware places small CTAs several to an SM before it moves on, and co-resident CTAs of this kernel slow one
+  // another (measured, H with dropout at K = 2560: M = 8192 as 128 four-slab CTAs 35.9 us packed, 24.0 us one per SM;
+  // M = 4096 as 128 two-slab CTAs 29.9 / 18.8 us).
+  size_t smem = skinny::rp_smem_bytes<RP, SLABS>();
+  if (grid <= 148) smem = std::max<size_t>(smem, skinny::RP_ONE_PER_SM_BYTES);
   CUDA_TRY(launch_pdl(skinny::rowproj_kernel<BF, RP, DIRECT, NBE, SLABS>, dim3(grid), dim3(skinny::rp_threads(RP, SLABS)),
-                      skinny::rp_smem_bytes<RP, SLABS>(), stream, 1, tmAct, tmP, p));
+                      smem, stream, 1, tmAct, tmP, p));
   return 0;
 }
 // 16-row slabs per CTA by M (skinny::rp_slabs_for): the tensor map of the activation was built for the same box
