@@ -94,7 +94,8 @@ FWD_BWD_CASES = [
     (1300, 768, 2304, 32, 0.05, True, torch.float16, True),
     # more column tiles than SMs in the column projection (152 + 6 tiles of 128: one split each, two waves)
     (256, 768, 19456, 8, 0.05, False, torch.bfloat16, False),
-    # row-projection CTAs: 1 slab up to 2368 rows, 2 up to 4736 (the 2400-row case above), 4 beyond (these two, ragged M)
+    # row projections: up to 4736 rows the one-slab, eight-warp kernel (every case above), beyond it the four-slab one
+    # (these two, ragged M, fewer CTAs than SMs; the full-size tests have more)
     (5000, 768, 768, 8, 0.05, True, torch.bfloat16, True),
     (4800, 2560, 2560, 64, 0.05, False, torch.float16, False),
 ]

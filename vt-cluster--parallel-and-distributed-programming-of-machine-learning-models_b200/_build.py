@@ -10,7 +10,7 @@ REPO_ROOT = os.path.dirname(PKG_DIR)
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "liblora_b200.so")
 SOURCES = ["lora_b200.cu"]
-HEADERS = ["common.cuh", "colproj_sm100.cuh", "gemm_sm100.cuh", "gemm_masked_sm100.cuh", "skinny.cuh", "act.cuh", "ce.cuh", "p2p.cuh", "optim.cuh"]
+HEADERS = ["common.cuh", "colproj_sm100.cuh", "rowproj_small.cuh", "gemm_sm100.cuh", "gemm_masked_sm100.cuh", "skinny.cuh", "act.cuh", "ce.cuh", "p2p.cuh", "optim.cuh"]
 
 
 def _stale() -> bool:

@@ -22,6 +22,7 @@
 #include "gemm_masked_sm100.cuh"
 #include "lora_b200.h"
 #include "optim.cuh"
+#include "rowproj_small.cuh"
 #include "skinny.cuh"
 
 namespace {
@@ -196,12 +197,10 @@ int device_setup(int* sm_count) {
     CUDA_TRY(opt_in_smem(gemm::gemm_masked_kernel, gemm::SMEM_BYTES));
 #define OPT_IN_SKINNY(BF, RP)                                                                                       \
   CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP, false, 2, 4>, skinny::rp_smem_optin<RP, 4>()));               \
-  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP, false, 2, 2>, skinny::rp_smem_optin<RP, 2>()));               \
-  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, RP, false, 2, 1>, skinny::rp_smem_optin<RP, 1>()));
+  CUDA_TRY(opt_in_smem(skinny::rowproj_small_kernel<BF, RP, false, 2>, skinny::RP_ONE_PER_SM_BYTES));
 #define OPT_IN_DIRECT(BF, NBE)                                                                                      \
   CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, 16, true, NBE, 4>, skinny::rp_smem_optin<16, 4>()));              \
-  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, 16, true, NBE, 2>, skinny::rp_smem_optin<16, 2>()));              \
-  CUDA_TRY(opt_in_smem(skinny::rowproj_kernel<BF, 16, true, NBE, 1>, skinny::rp_smem_optin<16, 1>()));
+  CUDA_TRY(opt_in_smem(skinny::rowproj_small_kernel<BF, 16, true, NBE>, skinny::RP_ONE_PER_SM_BYTES));
     CUDA_TRY(opt_in_smem(skinny::colproj_umma_kernel<16>, skinny::cu_smem_bytes<16>()));
     CUDA_TRY(opt_in_smem(skinny::colproj_umma_kernel<32>, skinny::cu_smem_bytes<32>()));
     CUDA_TRY(opt_in_smem(skinny::colproj_umma_kernel<64>, skinny::cu_smem_bytes<64>()));
@@ -346,15 +345,27 @@ int launch_rowproj_s(const CUtensorMap& tmAct, const CUtensorMap& tmP, const ski
                       smem, stream, 1, tmAct, tmP, p));
   return 0;
 }
-// 16-row slabs per CTA by M (skinny::rp_slabs_for): the tensor map of the activation was built for the same box
+// Few rows (rowproj_small.cuh): one 16-row slab per CTA, eight warps splitting the columns.  At most 296 CTAs; the
+// shared-memory request keeps them to one (<= 148 CTAs) or two per SM.
+constexpr int64_t kRowprojSmallMaxM = 296 * 16;
+template <bool BF, int RP, bool DIRECT, int NBE>
+int launch_rowproj_small(const CUtensorMap& tmAct, const CUtensorMap& tmP, const skinny::RowProjParams& p,
+                         cudaStream_t stream) {
+  const int grid = (p.M + 15) / 16;
+  size_t smem = skinny::rs_smem_bytes<RP>();
+  smem = std::max<size_t>(smem, grid <= 148 ? skinny::RP_ONE_PER_SM_BYTES : 80 * 1024);
+  CUDA_TRY(launch_pdl(skinny::rowproj_small_kernel<BF, RP, DIRECT, NBE>, dim3(grid), dim3(skinny::RS_THREADS), smem, stream, 1,
+                      tmAct, tmP, p));
+  return 0;
+}
+// The tensor map of the activation was built for the same box (rowproj_box_rows).
 template <bool BF, int RP, bool DIRECT = false, int NBE = 2>
 int launch_rowproj_t(const CUtensorMap& tmAct, const CUtensorMap& tmP, const skinny::RowProjParams& p,
                      cudaStream_t stream) {
-  const int slabs = skinny::rp_slabs_for(p.M);
-  if (slabs == 4) return launch_rowproj_s<BF, RP, DIRECT, NBE, 4>(tmAct, tmP, p, stream);
-  if (slabs == 2) return launch_rowproj_s<BF, RP, DIRECT, NBE, 2>(tmAct, tmP, p, stream);
-  return launch_rowproj_s<BF, RP, DIRECT, NBE, 1>(tmAct, tmP, p, stream);
+  if (p.M <= kRowprojSmallMaxM) return launch_rowproj_small<BF, RP, DIRECT, NBE>(tmAct, tmP, p, stream);
+  return launch_rowproj_s<BF, RP, DIRECT, NBE, 4>(tmAct, tmP, p, stream);
 }
+int rowproj_box_rows(int64_t M) { return M <= kRowprojSmallMaxM ? 16 : skinny::rp_rows(4); }
 
 // Forward with padded rank 16 and the fp32 masters at hand: the row projection reads A directly and packs A, B
 // for the kernels after it (no separate pack launch).
@@ -375,7 +386,7 @@ int launch_rowproj(const void* act, const void* P, void* out, uint8_t* keep_out,
                    const uint64_t* offset_dev = nullptr, unsigned int* zero_words = nullptr, int n_zero_words = 0,
                    const DirectPack* direct = nullptr) {
   CUtensorMap tmAct, tmP;
-  if (make_tmap(&tmAct, act, dtype, C, M, C, skinny::RP_BK, skinny::rp_rows(skinny::rp_slabs_for(M)), CU_TENSOR_MAP_SWIZZLE_128B,
+  if (make_tmap(&tmAct, act, dtype, C, M, C, skinny::RP_BK, rowproj_box_rows(M), CU_TENSOR_MAP_SWIZZLE_128B,
                 "rowproj act"))
     return 1;
   if (direct) {  // the fp32 master A [r, C]: boxes of 32 columns (one 128-byte swizzle row) x 8 or 16 rank rows

@@ -113,15 +113,11 @@ __global__ void pack_adapters_kernel(const float* __restrict__ A, const float* _
 // 16-row slabs per CTA.  Measured on B200 (M = 16384, C = 2560, r_pad 16, round 1): 4 slabs (64 rows,
 // 256 CTAs) beat 1 slab (1024 small CTAs: every CTA re-reads the P tiles from L2 and 2 KiB TMA boxes
 // are inefficient) and 7 slabs (147 CTAs, one per SM: too few warps per SM).
-// kSlabs is a template parameter: 4 whenever that fills the GPU (M >= 148 x 64 rows); below that the smallest of
-// 1 / 2 / 4 that needs no more CTAs than there are SMs, and the launch gives each CTA an SM of its own (lora_b200.cu,
-// launch_rowproj_s): M = 4096 as 64 four-slab CTAs put the whole generator on 64 of the 148 SMs (35.7 us, the time
-// of M = 16384); as 128 two-slab CTAs, one per SM, 18.8 us.
+// kSlabs is a template parameter; the library runs 4 (few rows go to rowproj_small.cuh: one slab per CTA, eight warps
+// splitting the columns).  Measured on the way, H with dropout at K = 2560: M = 4096 as 64 four-slab CTAs 35.7 us (the
+// hardware packs small CTAs several to an SM, so the generator ran on 32-64 SMs), as 128 two-slab CTAs with an SM
+// each 18.8 us; seven-slab CTAs, one per SM, at M = 16384: 35.2 against 36.2 us.
 __host__ __device__ constexpr int rp_rows(int slabs) { return 16 * slabs; }
-inline int rp_slabs_for(long long M) {
-  if (M >= 148 * 64) return 4;  // (seven-slab CTAs, one per SM, at M = 16384: 35.2 against 36.2 us -- not kept)
-  return M <= 148 * 16 ? 1 : (M <= 148 * 32 ? 2 : 4);
-}
 constexpr int RP_ONE_PER_SM_BYTES = 116 * 1024;  // more than half of an SM's 227 KiB: at most one CTA per SM
 // Padded rank 64 needs ~123 registers per thread (32 accumulators, 16 B-fragment words).  ptxas sizes the register
 // file for the warp count rounded up to an even number, so nine warps cap a 2-CTA/SM kernel at 96; with EIGHT warps
