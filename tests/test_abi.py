@@ -37,6 +37,25 @@ def test_host_only_entry_points(pkg):
     assert b.lib().lora_last_error() == b""
 
 
+def test_workspace_plan_is_one_wave(pkg):
+    """The backward's scratch = dH [M, rp] (16-bit) + two counter tables + the split partial sums of dB and dA.  The
+    column projection plans ONE wave of at most 148 CTAs (lora_b200.cu, colproj_plan), so the partial sums can never
+    exceed 148 column-tile-splits of 128 columns x rp fp32 (plus what a single split needs when there are more column
+    tiles than SMs) -- a host-only property of the planner, checked over the sweep's shapes and some ragged ones."""
+    b = pkg.binding
+    for (M, K, N, r) in [(16384, 2560, 2560, 8), (16384, 2560, 10240, 64), (4096, 10240, 2560, 16), (65536, 768, 2304, 64),
+                         (130, 776, 520, 33), (1, 8, 8, 1), (2048, 2560, 2560, 8), (256, 768, 19456, 8), (300, 3072, 768, 24)]:
+        rp = b.rpad(r)
+        w = b.workspace_bytes(M, K, N, r)
+        fixed = ((M * rp * 2 + 255) // 256) * 256 + 2 * 4096 * 4
+        tiles = -(-K // 128) + -(-N // 128)
+        one_split = (K + N) * rp * 4
+        wave = 148 * 128 * rp * 4
+        assert fixed + one_split <= w <= fixed + max(one_split, wave) + (K + N) * rp * 4 + 1024, (M, K, N, r, w)
+        if tiles > 148:
+            assert w <= fixed + one_split + 1024
+
+
 def test_no_cpu_fallback(pkg):
     x = torch.zeros(8, 16, dtype=torch.bfloat16)
     with pytest.raises(RuntimeError, match="no CPU fallback"):
